@@ -1,0 +1,454 @@
+// Dense path: persistent, warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   C[M, N] = epilogue( A[M, K] . B[N, K]^T ),  bf16 operands, fp32 accumulation in TMEM.
+//
+// * warp 0: TMA producer (A and B tiles, 128-byte swizzle, ring of kStages smem slots)
+// * warp 1: TMEM allocation + single-thread tcgen05.mma issue, tcgen05.commit to mbarriers
+// * warps 2-5: epilogue, one accumulator row (TMEM lane) per thread, fused element-wise work
+// The accumulator is double buffered in TMEM (except BLOCK_N = 512) so the epilogue of tile i
+// overlaps the main loop of tile i+1.  With A_MODE = 1 the A operand is gathered by 4-D TMA boxes
+// from an NHWC activation tensor (implicit-GEMM 3x3 convolution; out-of-bounds box elements are
+// zero-filled by TMA, which implements the zero padding).
+//
+// Replaces the cuDNN / cuBLAS calls behind nn.Conv2d and nn.Linear on the reference path
+// (reference: gluefactory/models/extractors/superpoint_open.py:59-115,
+//  gluefactory/models/matchers/lightglue.py:125-215,265-281).
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace b200 {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
+constexpr int kTileH = 8, kTileW = 16;  // conv M-tile: 8 x 16 pixels
+constexpr int kGemmThreads = 192;
+
+template <int BLOCK_N>
+struct GemmCfg {
+    static constexpr int kABytes = kBlockM * kBlockK * 2;
+    static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = (200 * 1024 / kStageBytes) > 8 ? 8 : (200 * 1024 / kStageBytes);
+    static constexpr int kAccStages = BLOCK_N <= 256 ? 2 : 1;
+    static constexpr int kAccStride = BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : (BLOCK_N <= 256 ? 256 : 512));
+    static constexpr int kTmemCols = kAccStride * kAccStages < 32 ? 32 : kAccStride * kAccStages;
+    static constexpr int kUmmaN = BLOCK_N > 256 ? 256 : BLOCK_N;
+    static constexpr int kNumUmmaN = BLOCK_N / kUmmaN;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static_assert(kStageBytes % 1024 == 0, "stage must keep 1024-byte alignment for SWIZZLE_128B");
+    static_assert(kTmemCols <= 512, "TMEM budget");
+};
+
+__device__ __forceinline__ float gelu_erf(float x) {
+    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+__device__ __forceinline__ void store16B(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    *reinterpret_cast<uint4*>(p) = make_uint4(a, b, c, d);
+}
+
+// ---------------------------------------------------------------------------------------------
+// epilogue bodies: `acc_taddr` addresses column 0 of this tile's accumulator for this warp's lanes
+// ---------------------------------------------------------------------------------------------
+template <int BLOCK_N, int EPI>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_taddr, int batch,
+                                              long long row_in_batch, bool row_valid, int n0, int lane,
+                                              int img, int py, int px) {
+    uint32_t r[32];
+    if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_QKV_ROTARY || EPI == EPI_RESID || EPI == EPI_F32) {
+        const long long grow = (long long)batch * p.M + row_in_batch;  // global output row
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            const int col0 = n0 + c * 32;
+            if (col0 >= p.N) break;  // warp-uniform
+            tmem_ld32(acc_taddr + c * 32, r);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                v[i] = __uint_as_float(r[i]);
+                if (EPI == EPI_F32) v[i] *= p.alpha;
+                if (p.bias != nullptr && col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
+            }
+            if constexpr (EPI == EPI_QKV_ROTARY) {
+                if (col0 < p.rot_cols && row_valid) {
+                    const float2* cs = p.cs + grow * 32 + ((col0 & 63) >> 1);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float2 t = __ldg(cs + i);
+                        const float x0 = v[2 * i], x1 = v[2 * i + 1];
+                        v[2 * i] = x0 * t.x - x1 * t.y;
+                        v[2 * i + 1] = x1 * t.x + x0 * t.y;
+                    }
+                }
+            }
+            if (!row_valid) continue;
+            if constexpr (EPI == EPI_RESID) {
+                float* o32 = p.out32 + grow * p.ld32 + col0;
+                const float* rs = p.resid + grow * p.ld32 + col0;
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    const float4 t = *reinterpret_cast<const float4*>(rs + i);
+                    v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
+                    *reinterpret_cast<float4*>(o32 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+                }
+            }
+            if constexpr (EPI == EPI_F32) {
+                float* o32 = p.out32 + (long long)batch * p.out32_batch_stride + row_in_batch * p.ld32 + col0;
+                if ((p.ld32 & 3) == 0 && col0 + 32 <= p.N) {
+#pragma unroll
+                    for (int i = 0; i < 32; i += 4)
+                        *reinterpret_cast<float4*>(o32 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (col0 + i < p.N) o32[i] = v[i];
+                }
+            } else {
+                __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col0;
+#pragma unroll
+                for (int i = 0; i < 32; i += 8)
+                    store16B(o16 + i, pack_bf16(v[i], v[i + 1]), pack_bf16(v[i + 2], v[i + 3]),
+                             pack_bf16(v[i + 4], v[i + 5]), pack_bf16(v[i + 6], v[i + 7]));
+            }
+        }
+    } else if constexpr (EPI == EPI_LN_GELU) {
+        // two passes over the 512 accumulator columns of this row: statistics, then normalise
+        float sum = 0.f, sumsq = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            tmem_ld32(acc_taddr + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float x = __uint_as_float(r[i]) + __ldg(p.bias + c * 32 + i);
+                sum += x;
+                sumsq += x * x;
+            }
+        }
+        const float mean = sum * (1.0f / BLOCK_N);
+        const float var = fmaxf(sumsq * (1.0f / BLOCK_N) - mean * mean, 0.f);
+        const float rstd = rsqrtf(var + p.ln_eps);
+        __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) + row_in_batch * p.ld16;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            tmem_ld32(acc_taddr + c * 32, r);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int col = c * 32 + i;
+                const float x = __uint_as_float(r[i]) + __ldg(p.bias + col);
+                v[i] = gelu_erf((x - mean) * rstd * __ldg(p.ln_gamma + col) + __ldg(p.ln_beta + col));
+            }
+            if (row_valid) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 8)
+                    store16B(o16 + c * 32 + i, pack_bf16(v[i], v[i + 1]), pack_bf16(v[i + 2], v[i + 3]),
+                             pack_bf16(v[i + 4], v[i + 5]), pack_bf16(v[i + 6], v[i + 7]));
+            }
+        }
+    } else if constexpr (EPI == EPI_CONV_RELU_BN) {
+        // pixel (img, py, px); with pooling the 2x2 partners are lanes ^1 (x) and ^16 (y)
+        const bool store_lane = p.pool ? ((lane & 17) == 0) : true;
+        const int oy = p.pool ? (py >> 1) : py, ox = p.pool ? (px >> 1) : px;
+        const int OH = p.pool ? (p.H >> 1) : p.H, OW = p.pool ? (p.W >> 1) : p.W;
+        const bool ok = row_valid && store_lane && oy < OH && ox < OW;
+        __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) +
+                             (((long long)img * OH + oy) * OW + ox) * p.ld16 + n0;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            tmem_ld32(acc_taddr + c * 32, r);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int col = n0 + c * 32 + i;
+                float x = __uint_as_float(r[i]) + __ldg(p.bias + col);
+                if (p.relu) x = fmaxf(x, 0.f);
+                x = x * __ldg(p.scale + col) + __ldg(p.shift + col);
+                if (p.pool) {
+                    x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
+                    x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 16));
+                }
+                v[i] = x;
+            }
+            if (ok) {
+#pragma unroll
+                for (int i = 0; i < 32; i += 8)
+                    store16B(o16 + c * 32 + i, pack_bf16(v[i], v[i + 1]), pack_bf16(v[i + 2], v[i + 3]),
+                             pack_bf16(v[i + 4], v[i + 5]), pack_bf16(v[i + 6], v[i + 7]));
+            }
+        }
+    } else if constexpr (EPI == EPI_CONV_BN_L2) {
+        float sumsq = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            tmem_ld32(acc_taddr + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int col = c * 32 + i;
+                const float x = (__uint_as_float(r[i]) + __ldg(p.bias + col)) * __ldg(p.scale + col) +
+                                __ldg(p.shift + col);
+                sumsq += x * x;
+            }
+        }
+        const float inv = 1.0f / fmaxf(sqrtf(sumsq), 1e-12f);
+        float* o32 = p.out32 + row_in_batch * p.ld32;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N / 32; ++c) {
+            tmem_ld32(acc_taddr + c * 32, r);
+            tmem_ld_wait();
+            if (!row_valid) continue;
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                float v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int col = c * 32 + i + j;
+                    v[j] = ((__uint_as_float(r[i + j]) + __ldg(p.bias + col)) * __ldg(p.scale + col) +
+                            __ldg(p.shift + col)) * inv;
+                }
+                *reinterpret_cast<float4*>(o32 + c * 32 + i) = make_float4(v[0], v[1], v[2], v[3]);
+            }
+        }
+    } else if constexpr (EPI == EPI_CONV_BN_SOFTMAX_D2S) {
+        // 65 logits per cell (columns 0..64 of an 80-wide tile)
+        float v[80];
+        uint32_t q[16];
+        tmem_ld32(acc_taddr, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+        tmem_ld32(acc_taddr + 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[32 + i] = __uint_as_float(r[i]);
+        tmem_ld16(acc_taddr + 64, q);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[64 + i] = __uint_as_float(q[i]);
+        float mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 65; ++i) {
+            v[i] = (v[i] + __ldg(p.bias + i)) * __ldg(p.scale + i) + __ldg(p.shift + i);
+            mx = fmaxf(mx, v[i]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < 65; ++i) {
+            v[i] = expf(v[i] - mx);
+            sum += v[i];
+        }
+        if (row_valid) {
+            const int cells = p.cells_h * p.cells_w;
+            const int im = (int)(row_in_batch / cells);
+            const int rem = (int)(row_in_batch - (long long)im * cells);
+            const int cy = rem / p.cells_w, cx = rem - cy * p.cells_w;
+            const long long hw = (long long)p.cells_w * 8;
+            float* o = p.out32 + ((long long)im * p.cells_h * 8 + cy * 8) * hw + cx * 8;
+#pragma unroll
+            for (int dy = 0; dy < 8; ++dy) {
+                float* row = o + dy * hw;
+                *reinterpret_cast<float4*>(row) = make_float4(v[dy * 8] / sum, v[dy * 8 + 1] / sum,
+                                                              v[dy * 8 + 2] / sum, v[dy * 8 + 3] / sum);
+                *reinterpret_cast<float4*>(row + 4) = make_float4(v[dy * 8 + 4] / sum, v[dy * 8 + 5] / sum,
+                                                                  v[dy * 8 + 6] / sum, v[dy * 8 + 7] / sum);
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel
+// ---------------------------------------------------------------------------------------------
+template <int BLOCK_N, int EPI, int A_MODE>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const GemmParams p) {
+    using Cfg = GemmCfg<BLOCK_N>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* empty_bar = full_bar + Cfg::kStages;
+    uint64_t* acc_full = empty_bar + Cfg::kStages;
+    uint64_t* acc_empty = acc_full + Cfg::kAccStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + Cfg::kAccStages);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
+    const int n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
+    const long long total_tiles = (long long)p.batch * m_tiles * n_tiles;
+    const int k_blocks = p.K / kBlockK;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tensormap(&tmap_a);
+        prefetch_tensormap(&tmap_b);
+        for (int s = 0; s < Cfg::kStages; ++s) {
+            mbar_init(full_bar + s, 1);
+            mbar_init(empty_bar + s, 1);
+        }
+        for (int s = 0; s < Cfg::kAccStages; ++s) {
+            mbar_init(acc_full + s, 1);
+            mbar_init(acc_empty + s, 4);  // one arrival per epilogue warp
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                const int nt = (int)(t % n_tiles);
+                const long long rest = t / n_tiles;
+                const int mt = (int)(rest % m_tiles);
+                const int b = (int)(rest / m_tiles);
+                const int brow = b * p.b_batch_rows + nt * BLOCK_N;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(empty_bar + stage, phase ^ 1);
+                    uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                    uint8_t* sb = sa + Cfg::kABytes;
+                    mbar_arrive_expect_tx(full_bar + stage, Cfg::kStageBytes);
+                    if constexpr (A_MODE == 0) {
+                        tma_load_2d(sa, &tmap_a, full_bar + stage, kb * kBlockK, b * p.a_batch_rows + mt * kBlockM);
+                    } else {
+                        const int cblocks = p.Cin / kBlockK;
+                        const int tap = kb / cblocks, cb = kb - tap * cblocks;
+                        const int ty = mt / p.tiles_x, tx = mt - ty * p.tiles_x;
+                        tma_load_4d(sa, &tmap_a, full_bar + stage, cb * kBlockK, tx * kTileW + (tap % 3) - 1,
+                                    ty * kTileH + (tap / 3) - 1, b);
+                    }
+#pragma unroll
+                    for (int h = 0; h < Cfg::kNumUmmaN; ++h)
+                        tma_load_2d(sb + h * Cfg::kUmmaN * kBlockK * 2, &tmap_b, full_bar + stage, kb * kBlockK,
+                                    brow + h * Cfg::kUmmaN);
+                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(kBlockM, Cfg::kUmmaN, 1u, 0u, 0u);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                mbar_wait(acc_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(full_bar + stage, phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+                    const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+                    for (int k = 0; k < kBlockK / 16; ++k) {
+                        const uint64_t adesc = umma_smem_desc_sw128(sa + k * 32, 1024, 16);
+#pragma unroll
+                        for (int h = 0; h < Cfg::kNumUmmaN; ++h) {
+                            const uint64_t bdesc =
+                                umma_smem_desc_sw128(sb + h * Cfg::kUmmaN * kBlockK * 2 + k * 32, 1024, 16);
+                            umma_f16(d_tmem + h * Cfg::kUmmaN, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(empty_bar + stage);  // frees the smem slot once these MMAs retire
+                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(acc_full + acc);
+                if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================== epilogue warps (TMEM lanes 32*(warp%4) ..) =====================
+        const int quarter = warp & 3;
+        const int r_in_tile = quarter * 32 + lane;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            const int nt = (int)(t % n_tiles);
+            const long long rest = t / n_tiles;
+            const int mt = (int)(rest % m_tiles);
+            const int b = (int)(rest / m_tiles);
+            long long row_in_batch = 0;
+            bool row_valid;
+            int py = 0, px = 0;
+            if constexpr (A_MODE == 1) {
+                const int ty = mt / p.tiles_x, tx = mt - ty * p.tiles_x;
+                py = ty * kTileH + (r_in_tile >> 4);
+                px = tx * kTileW + (r_in_tile & 15);
+                row_valid = py < p.H && px < p.W;
+            } else {
+                row_in_batch = (long long)mt * kBlockM + r_in_tile;
+                row_valid = row_in_batch < p.M;
+            }
+            mbar_wait(acc_full + acc, acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + ((uint32_t)(quarter * 32) << 16);
+            epilogue_tile<BLOCK_N, EPI>(p, taddr, b, row_in_batch, row_valid, nt * BLOCK_N, lane, b, py, px);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty + acc);
+            if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host launcher
+// ---------------------------------------------------------------------------------------------
+template <int BLOCK_N, int EPI, int A_MODE>
+static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int num_sms,
+                      cudaStream_t stream) {
+    using Cfg = GemmCfg<BLOCK_N>;
+    auto kern = gemm_tcgen05_kernel<BLOCK_N, EPI, A_MODE>;
+    static bool configured = false;
+    if (!configured) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+        configured = true;
+    }
+    const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
+    const int n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
+    const long long total = (long long)p.batch * m_tiles * n_tiles;
+    if (total == 0) return 0;
+    const int grid = (int)(total < num_sms ? total : num_sms);
+    kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, p);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const CUtensorMap& tb,
+                const GemmParams& p, int num_sms, cudaStream_t stream) {
+    B200_REQUIRE(p.K > 0 && p.K % kBlockK == 0, "gemm: K=%d must be a positive multiple of 64", p.K);
+#define B200_CASE(BN, E, AM) \
+    if (block_n == BN && epi == E && a_mode == AM) return launch_one<BN, E, AM>(ta, tb, p, num_sms, stream);
+    B200_CASE(256, EPI_BIAS_BF16, 0)
+    B200_CASE(256, EPI_QKV_ROTARY, 0)
+    B200_CASE(512, EPI_LN_GELU, 0)
+    B200_CASE(256, EPI_RESID, 0)
+    B200_CASE(128, EPI_F32, 0)
+    B200_CASE(256, EPI_F32, 0)
+    B200_CASE(64, EPI_CONV_RELU_BN, 1)
+    B200_CASE(128, EPI_CONV_RELU_BN, 1)
+    B200_CASE(256, EPI_CONV_RELU_BN, 1)
+    B200_CASE(256, EPI_CONV_BN_L2, 0)
+    B200_CASE(80, EPI_CONV_BN_SOFTMAX_D2S, 0)
+#undef B200_CASE
+    set_last_error("gemm: no kernel instance for block_n=%d epi=%d a_mode=%d", block_n, epi, a_mode);
+    return -1;
+}
+
+}  // namespace b200

@@ -1,0 +1,16 @@
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+int launch_conv1a(const float* img, int B, int C, int H, int W, const float* w, const float* bias,
+                  const float* scale, const float* shift, void* out, cudaStream_t stream);
+int launch_nms_border(const float* scores, int B, int H, int W, int radius, int pad, float* out,
+                      cudaStream_t stream);
+int launch_select_topk(const float* nms_map, int B, int H, int W, float threshold, int k, float* kpts,
+                       float* kscores, int* kidx, int* counts, cudaStream_t stream);
+int launch_count_candidates(const float* nms_map, int B, int H, int W, float threshold, int* counts,
+                            cudaStream_t stream);
+int launch_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* kpts, int K,
+                              int stride_px, float* out, cudaStream_t stream);
+}  // namespace b200
