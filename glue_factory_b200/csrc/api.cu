@@ -1,0 +1,266 @@
+// C-ABI entry points (include/b200glue.h): argument checks, TMA tensor-map construction, launches.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+
+#include "../../include/b200glue.h"
+#include "attention.cuh"
+#include "common.cuh"
+#include "gemm.cuh"
+#include "lg_kernels.cuh"
+#include "sp_kernels.cuh"
+
+namespace b200 {
+
+static thread_local char g_error[512] = "";
+
+void set_last_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const CUtensorMap& tb,
+                const GemmParams& p, int num_sms, cudaStream_t stream);
+int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
+                     int num_seqs, int max_q_len, int heads, cudaStream_t stream);
+
+// ---------------------------------------------------------------------------------------------
+// driver entry point for cuTensorMapEncodeTiled (no link-time dependency on libcuda)
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+struct MapKey {
+    const void* ptr;
+    uint64_t d[4];
+    uint64_t s[3];
+    uint32_t box[4];
+    uint32_t rank;
+    bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+        uint64_t h = 1469598103934665603ull;
+        for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ w[i]) * 1099511628211ull;
+        return (size_t)h;
+    }
+};
+static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+static std::mutex g_maps_mu;
+
+// bf16 tensor of `rank` dims (dim 0 contiguous), 128-byte swizzle, zero fill out of bounds
+static int make_map(CUtensorMap* out, const void* ptr, uint32_t rank, const uint64_t* dims,
+                    const uint64_t* strides_bytes /*rank-1*/, const uint32_t* box) {
+    MapKey key;
+    memset(&key, 0, sizeof(key));
+    key.ptr = ptr;
+    key.rank = rank;
+    for (uint32_t i = 0; i < rank; ++i) { key.d[i] = dims[i]; key.box[i] = box[i]; }
+    for (uint32_t i = 0; i + 1 < rank; ++i) key.s[i] = strides_bytes[i];
+    {
+        std::lock_guard<std::mutex> lk(g_maps_mu);
+        auto it = g_maps.find(key);
+        if (it != g_maps.end()) { *out = it->second; return 0; }
+    }
+    EncodeTiledFn enc = get_encode_fn();
+    B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand %p is not 16-byte aligned", ptr);
+    for (uint32_t i = 0; i + 1 < rank; ++i)
+        B200_REQUIRE(strides_bytes[i] % 16 == 0, "TMA stride %llu is not a multiple of 16 bytes",
+                     (unsigned long long)strides_bytes[i]);
+    cuuint64_t gd[4];
+    cuuint64_t gs[3];
+    cuuint32_t bx[4], es[4] = {1, 1, 1, 1};
+    for (uint32_t i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; }
+    for (uint32_t i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
+    const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gd, gs, bx, es,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code %d (rank %u, dims %llu x %llu, box %u x %u)",
+                 (int)r, rank, (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1]);
+    std::lock_guard<std::mutex> lk(g_maps_mu);
+    if (g_maps.size() > 4096) g_maps.clear();
+    g_maps.emplace(key, *out);
+    return 0;
+}
+
+// [rows, cols] bf16 matrix with leading dimension ld (elements); box = 64 columns x box_rows rows
+static int make_map_2d(CUtensorMap* out, const void* ptr, long long rows, long long cols, long long ld,
+                       uint32_t box_rows) {
+    const uint64_t dims[2] = {(uint64_t)cols, (uint64_t)rows};
+    const uint64_t strides[1] = {(uint64_t)ld * 2};
+    const uint32_t box[2] = {64, box_rows};
+    return make_map(out, ptr, 2, dims, strides, box);
+}
+
+static int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 0;
+    }
+    return n;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_abi_version(void) { return B200_ABI_VERSION; }
+const char* b200_last_error(void) { return g_error; }
+
+int b200_sm_count(int* out) {
+    const int n = sm_count();
+    B200_REQUIRE(n > 0, "no CUDA device available");
+    *out = n;
+    return 0;
+}
+
+int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    B200_REQUIRE(d != nullptr, "gemm: null descriptor");
+    B200_REQUIRE(d->a && d->b, "gemm: null operand");
+    const int num_sms = sm_count();
+    B200_REQUIRE(num_sms > 0, "gemm: no CUDA device available");
+    GemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = d->M; p.N = d->N; p.K = d->K; p.batch = d->batch;
+    p.a_batch_rows = d->a_batch_rows; p.b_batch_rows = d->b_batch_rows;
+    p.bias = d->bias; p.scale = d->scale; p.shift = d->shift;
+    p.relu = d->relu; p.pool = d->pool; p.alpha = d->alpha;
+    p.resid = d->resid; p.cs = reinterpret_cast<const float2*>(d->cossin); p.rot_cols = d->rot_cols;
+    p.ln_gamma = d->ln_gamma; p.ln_beta = d->ln_beta; p.ln_eps = d->ln_eps;
+    p.out16 = d->out16; p.ld16 = d->ld16; p.out32 = d->out32; p.ld32 = d->ld32;
+    p.out32_batch_stride = d->out32_batch_stride;
+    p.cells_h = d->cells_h; p.cells_w = d->cells_w;
+    B200_REQUIRE(d->batch >= 0 && d->N >= 1, "gemm: bad shape (batch=%d, N=%d)", d->batch, d->N);
+    if (d->batch == 0) return 0;
+
+    const int epi = d->epilogue;
+    if (epi == B200_EPI_BIAS_BF16 || epi == B200_EPI_QKV_ROTARY || epi == B200_EPI_LN_GELU ||
+        epi == B200_EPI_RESID || epi == B200_EPI_CONV_RELU_BN)
+        B200_REQUIRE(d->out16 != nullptr && (d->ld16 % 8) == 0 && (reinterpret_cast<uintptr_t>(d->out16) & 15) == 0,
+                     "gemm: bf16 output must be 16-byte aligned with ld %% 8 == 0");
+    if (epi == B200_EPI_RESID)
+        B200_REQUIRE(d->out32 && d->resid && (d->ld32 % 4) == 0 && d->N % 32 == 0, "gemm: bad residual epilogue operands");
+    if (epi == B200_EPI_BIAS_BF16 || epi == B200_EPI_QKV_ROTARY)
+        B200_REQUIRE(d->N % 32 == 0, "gemm: N=%d must be a multiple of 32 for bf16 epilogues", d->N);
+    if (epi == B200_EPI_QKV_ROTARY)
+        B200_REQUIRE(d->cossin != nullptr && d->rot_cols % 64 == 0, "gemm: rotary epilogue needs cos/sin and rot_cols %% 64 == 0");
+    if (epi == B200_EPI_LN_GELU)
+        B200_REQUIRE(d->N == 512 && d->block_n == 512 && d->bias && d->ln_gamma && d->ln_beta,
+                     "gemm: LayerNorm epilogue needs N == block_n == 512 and bias/gamma/beta");
+    if (epi == B200_EPI_F32) B200_REQUIRE(d->out32 != nullptr, "gemm: fp32 epilogue needs out32");
+    if (epi == B200_EPI_CONV_RELU_BN || epi == B200_EPI_CONV_BN_L2 || epi == B200_EPI_CONV_BN_SOFTMAX_D2S)
+        B200_REQUIRE(d->bias && d->scale && d->shift, "gemm: conv epilogues need bias, scale and shift");
+    if (epi == B200_EPI_CONV_BN_L2)
+        B200_REQUIRE(d->N == 256 && d->block_n == 256 && d->out32 && (d->ld32 % 4) == 0, "gemm: L2 epilogue needs N == 256");
+    if (epi == B200_EPI_CONV_BN_SOFTMAX_D2S)
+        B200_REQUIRE(d->N == 65 && d->block_n == 80 && d->out32 && d->cells_h > 0 && d->cells_w > 0 &&
+ d->M % (d->cells_h * d->cells_w) == 0,
+                     "gemm: softmax/depth-to-space epilogue needs N == 65, block_n == 80 and the cell grid");
+
+    CUtensorMap ta, tb;
+    const uint32_t b_box = d->block_n > 256 ? 256u : (uint32_t)d->block_n;
+    if (make_map_2d(&tb, d->b, d->b_rows, d->K, d->ldb, b_box) != 0) return -1;
+    int a_mode = 0;
+    if (d->conv) {
+        a_mode = 1;
+        B200_REQUIRE(d->Cin % 64 == 0 && d->K == 9 * d->Cin, "conv: Cin=%d must be a multiple of 64 and K == 9*Cin", d->Cin);
+        B200_REQUIRE(d->N % d->block_n == 0, "conv: Cout=%d must be a multiple of block_n=%d", d->N, d->block_n);
+        p.H = d->H; p.W = d->W; p.Cin = d->Cin;
+        p.tiles_x = (d->W + 15) / 16; p.tiles_y = (d->H + 7) / 8;
+        const uint64_t dims[4] = {(uint64_t)d->Cin, (uint64_t)d->W, (uint64_t)d->H, (uint64_t)d->batch};
+        const uint64_t strides[3] = {(uint64_t)d->Cin * 2, (uint64_t)d->W * d->Cin * 2,
+                                     (uint64_t)d->H * d->W * d->Cin * 2};
+        const uint32_t box[4] = {64, 16, 8, 1};
+        if (make_map(&ta, d->a, 4, dims, strides, box) != 0) return -1;
+    } else {
+        B200_REQUIRE(d->M >= 1, "gemm: M=%d", d->M);
+        if (make_map_2d(&ta, d->a, d->a_rows, d->K, d->lda, 128) != 0) return -1;
+    }
+    return launch_gemm(d->block_n, epi, a_mode, ta, tb, p, num_sms, stream);
+}
+
+int b200_attention(const b200_attn_desc* d, b200_stream_t stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    B200_REQUIRE(d != nullptr && d->q && d->k && d->v && d->out && d->seqs, "attention: null argument");
+    B200_REQUIRE(d->heads >= 1 && d->num_seqs >= 0 && d->max_q_len >= 0, "attention: bad sizes");
+    B200_REQUIRE((d->ld_out % 8) == 0 && (d->out_col0 % 8) == 0 && (reinterpret_cast<uintptr_t>(d->out) & 15) == 0,
+                 "attention: output must be 16-byte aligned");
+    CUtensorMap tq, tk, tv;
+    if (make_map_2d(&tq, d->q, d->q_rows, d->ldq, d->ldq, 128) != 0) return -1;
+    if (make_map_2d(&tk, d->k, d->k_rows, d->ldk, d->ldk, 128) != 0) return -1;
+    if (make_map_2d(&tv, d->v, d->v_rows, d->ldv, d->ldv, 128) != 0) return -1;
+    AttnParams p;
+    p.seqs = reinterpret_cast<const AttnSeq*>(d->seqs);
+    p.len_override = d->len_override;
+    p.q_col0 = d->q_col0; p.k_col0 = d->k_col0; p.v_col0 = d->v_col0;
+    p.scale = d->scale;
+    p.out = d->out; p.ld_out = d->ld_out; p.out_col0 = d->out_col0;
+    return launch_attention(tq, tk, tv, p, d->num_seqs, d->max_q_len, d->heads, stream);
+}
+
+int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* w, const float* bias,
+                   const float* scale, const float* shift, void* out_nhwc, b200_stream_t stream) {
+    return launch_conv1a(image, B, C, H, W, w, bias, scale, shift, out_nhwc, static_cast<cudaStream_t>(stream));
+}
+int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders, float* out,
+                       b200_stream_t stream) {
+    return launch_nms_border(scores, B, H, W, nms_radius, remove_borders, out, static_cast<cudaStream_t>(stream));
+}
+int b200_sp_count_candidates(const float* nms_map, int B, int H, int W, float threshold, int* counts,
+                             b200_stream_t stream) {
+    return launch_count_candidates(nms_map, B, H, W, threshold, counts, static_cast<cudaStream_t>(stream));
+}
+int b200_sp_select_topk(const float* nms_map, int B, int H, int W, float threshold, int k, float* keypoints,
+                        float* scores, int* indices, int* counts, b200_stream_t stream) {
+    return launch_select_topk(nms_map, B, H, W, threshold, k, keypoints, scores, indices, counts,
+                              static_cast<cudaStream_t>(stream));
+}
+int b200_sp_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* keypoints, int K,
+                               int stride, float* out, b200_stream_t stream) {
+    return launch_sample_descriptors(dense, B, Hc, Wc, C, keypoints, K, stride, out, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_ingest(const float* desc, long long rows, float* x32, void* xm, long long ld_xm, b200_stream_t stream) {
+    return launch_ingest(desc, rows, x32, xm, ld_xm, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_posenc(const float* keypoints, const float* image_size, int B, int n, const float* wr,
+                   float* size_scratch, void* cossin, b200_stream_t stream) {
+    return launch_posenc(keypoints, image_size, B, n, wr, size_scratch, cossin, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_rowdot(const float* x32, long long rows, const float* w, const float* bias, int apply_sigmoid, float* out,
+                   b200_stream_t stream) {
+    return launch_rowdot(x32, rows, w, bias, apply_sigmoid, out, static_cast<cudaStream_t>(stream));
+}
+size_t b200_lg_assignment_workspace(int B, int M, int N) { return assignment_workspace_bytes(B, M, N); }
+int b200_lg_assignment(const float* sim, const float* z0, const float* z1, int B, int M, int N,
+                       float filter_threshold, void* workspace, float* scores, long long* matches0,
+                       long long* matches1, float* mscores0, float* mscores1, b200_stream_t stream) {
+    return launch_assignment(sim, z0, z1, B, M, N, filter_threshold, workspace, scores, matches0, matches1, mscores0,
+                             mscores1, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

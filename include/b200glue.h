@@ -1,0 +1,144 @@
+/* b200glue -- C ABI of the B200 (sm_100a) kernels behind Glue Factory's SuperPoint-open + LightGlue
+ * forward path.  Plain pointers and sizes only; no torch / pybind types.
+ *
+ * Conventions:
+ *  - every entry returns 0 on success, a negative code on failure; b200_last_error() gives the
+ *    thread-local message;
+ *  - all pointers are DEVICE pointers unless stated; outputs and workspaces are allocated by the caller;
+ *  - entries never allocate device memory, never synchronise, and enqueue on the given stream only.
+ *
+ * Each entry names the reference code it replaces (paths relative to the reference repository).
+ */
+#ifndef B200GLUE_H_
+#define B200GLUE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+int b200_abi_version(void);
+const char* b200_last_error(void);
+/* number of SMs of the current device (persistent kernels size their grid with it) */
+int b200_sm_count(int* out);
+
+/* ---- epilogue kinds of the dense tcgen05 GEMM ------------------------------------------------ */
+enum {
+    B200_EPI_BIAS_BF16 = 0,      /* nn.Linear: out16 = A.W^T + bias                                   */
+    B200_EPI_QKV_ROTARY = 1,     /* SelfBlock Wqkv + rotary on q,k      (lightglue.py:36-43,144-154)  */
+    B200_EPI_LN_GELU = 2,        /* ffn[0..2]: Linear -> LayerNorm -> GELU (lightglue.py:138-143)     */
+    B200_EPI_RESID = 3,          /* ffn[3] + residual add               (lightglue.py:157,213-214)    */
+    B200_EPI_F32 = 4,            /* MatchAssignment similarity einsum   (lightglue.py:276)            */
+    B200_EPI_CONV_RELU_BN = 5,   /* VGGBlock conv -> ReLU -> BN (+ MaxPool2d) (superpoint_open.py:59-105) */
+    B200_EPI_CONV_BN_L2 = 6,     /* descriptor head 1x1 + BN + F.normalize (superpoint_open.py:129-131) */
+    B200_EPI_CONV_BN_SOFTMAX_D2S = 7 /* detector head 1x1 + BN + softmax + depth-to-space (:134-140)  */
+};
+
+/* C[batch][M,N] = epilogue(A[batch][M,K] . B[batch][N,K]^T), bf16 operands (row-major, K contiguous). */
+typedef struct {
+    /* operands */
+    const void* a;      /* bf16, rows x K, leading dimension lda (elements)                             */
+    long long a_rows;   /* total rows addressable through `a` (all batches)                            */
+    long long lda;
+    const void* b;      /* bf16, rows x K, leading dimension ldb                                        */
+    long long b_rows;
+    long long ldb;
+    int M, N, K, batch;
+    int a_batch_rows, b_batch_rows; /* row offset between consecutive batches in a / b                */
+    int block_n;        /* N tile: 64, 80, 128, 256 or 512 (must match an instantiated kernel)         */
+    int epilogue;       /* B200_EPI_*                                                                   */
+    /* implicit-GEMM 3x3 convolution: set conv=1, `a` is NHWC [batch,H,W,Cin], K = 9*Cin               */
+    int conv, H, W, Cin;
+    /* epilogue operands (device pointers, fp32 unless noted; unused ones NULL)                        */
+    const float* bias;
+    const float* scale;
+    const float* shift;
+    int relu, pool;
+    float alpha;
+    const float* resid;     /* [M, ld32]                                                               */
+    const void* cossin;     /* float2 [M, 32] (cos, sin) per row and rotary frequency                  */
+    int rot_cols;
+    const float* ln_gamma;
+    const float* ln_beta;
+    float ln_eps;
+    void* out16;            /* bf16 output                                                             */
+    long long ld16;
+    float* out32;           /* fp32 output                                                             */
+    long long ld32;
+    long long out32_batch_stride;
+    int cells_h, cells_w;   /* D2S epilogue: rows are (image, cell_y, cell_x)                          */
+} b200_gemm_desc;
+
+/* nn.Linear / nn.Conv2d / einsum on the path -> tcgen05 GEMM (dense path). */
+int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream);
+
+/* One attention problem (see b200_attention). */
+typedef struct {
+    int q_row0, q_len, kv_row0, kv_len;
+    int q_len_slot, kv_len_slot; /* indices into len_override when it is non-NULL                      */
+} b200_attn_seq;
+
+/* softmax(scale * Q K^T) V for head_dim 64, heads laid out as 64-column slices of token-major bf16
+ * matrices.  Replaces Attention.forward / the CrossBlock einsum path (lightglue.py:105-122,186-215). */
+typedef struct {
+    const void* q; long long q_rows, ldq; int q_col0;
+    const void* k; long long k_rows, ldk; int k_col0;
+    const void* v; long long v_rows, ldv; int v_col0;
+    const b200_attn_seq* seqs; /* DEVICE array [num_seqs]                                              */
+    int num_seqs, max_q_len, heads;
+    const int* len_override;   /* optional DEVICE array of live sequence lengths (adaptive pruning)     */
+    float scale;
+    void* out; long long ld_out; int out_col0; /* bf16 [tokens, ld_out]                                */
+} b200_attn_desc;
+
+int b200_attention(const b200_attn_desc* d, b200_stream_t stream);
+
+/* ---- SuperPoint-open bandwidth kernels (superpoint_open.py) ---------------------------------- */
+/* first VGG block, C_in = 1 (or RGB -> gray first, :125-127): conv3x3 + bias + ReLU + BN, NHWC bf16 out */
+int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* w /*[64,9]*/,
+                   const float* bias, const float* scale, const float* shift, void* out_nhwc,
+                   b200_stream_t stream);
+/* batched_nms (:34-49) + border removal (:147-152); out has the shape of scores */
+int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
+                       float* out, b200_stream_t stream);
+/* number of pixels above the detection threshold per image (:155-160) */
+int b200_sp_count_candidates(const float* nms_map, int B, int H, int W, float threshold, int* counts,
+                             b200_stream_t stream);
+/* threshold + select_top_k_keypoints (:52-56,155-179): keypoints (x+0.5, y+0.5), scores, linear
+ * indices, per-image count = min(candidates, k).  Sorted by (score desc, index asc) when more than k
+ * candidates exist, row-major order otherwise. */
+int b200_sp_select_topk(const float* nms_map, int B, int H, int W, float threshold, int k,
+                        float* keypoints /*[B,k,2]*/, float* scores /*[B,k]*/, int* indices /*[B,k]*/,
+                        int* counts /*[B]*/, b200_stream_t stream);
+/* sample_descriptors (:20-31): dense is NHWC fp32 [B,Hc,Wc,256]; out [B,K,256] */
+int b200_sp_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* keypoints,
+                               int K, int stride, float* out, b200_stream_t stream);
+
+/* ---- LightGlue bandwidth kernels (lightglue.py) ---------------------------------------------- */
+/* fp32 descriptors -> fp32 residual stream x32 [rows,256] and bf16 copy xm[:, :256] (ld_xm elements) */
+int b200_lg_ingest(const float* desc, long long rows, float* x32, void* xm, long long ld_xm,
+                   b200_stream_t stream);
+/* normalize_keypoints (:21-33) + LearnableFourierPositionalEncoding (:46-59).  image_size [B,2] (w,h)
+ * or NULL (extent based; size_scratch [B,2] is then used).  out: float2 [B*n, 32] = (cos, sin). */
+int b200_lg_posenc(const float* keypoints, const float* image_size, int B, int n, const float* wr /*[32,2]*/,
+                   float* size_scratch, void* cossin, b200_stream_t stream);
+/* matchability / token-confidence logits (:62-73,283-284): out[row] = x[row,:256].w + bias, optional sigmoid */
+int b200_lg_rowdot(const float* x32, long long rows, const float* w, const float* bias, int apply_sigmoid,
+                   float* out, b200_stream_t stream);
+/* sigmoid_log_double_softmax (:250-262) + filter_matches (:287-303) */
+size_t b200_lg_assignment_workspace(int B, int M, int N);
+int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, const float* z1 /*[B,N]*/,
+                       int B, int M, int N, float filter_threshold, void* workspace,
+                       float* scores /*[B,M+1,N+1]*/, long long* matches0, long long* matches1,
+                       float* mscores0, float* mscores1, b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GLUE_H_ */
