@@ -1,0 +1,162 @@
+"""Launch wrappers: torch tensors in, raw pointers to the C ABI (include/b200glue.h).
+
+torch is used for device memory and streams only; every computation here is a kernel of
+libb200glue.so.  All wrappers enqueue on torch's current CUDA stream and never synchronise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import (  # noqa: F401
+    EPI_BIAS_BF16, EPI_CONV_BN_L2, EPI_CONV_BN_SOFTMAX_D2S, EPI_CONV_RELU_BN, EPI_F32, EPI_LN_GELU,
+    EPI_QKV_ROTARY, EPI_RESID, AttnDesc, AttnSeq, GemmDesc,
+)
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t, offset_elems: int = 0):
+    if t is None:
+        return None
+    return t.data_ptr() + offset_elems * t.element_size()
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise _lib.B200Error("b200glue kernels need CUDA tensors (there is no CPU fallback)")
+
+
+def gemm(a, w, *, M, N, K, lda, block_n, epilogue, a_rows=None, a_col0=0, ldb=None, batch=1,
+         a_batch_rows=0, b_batch_rows=0, b_row0=0, b_rows=None, conv=None, bias=None, scale=None, shift=None,
+         relu=0, pool=0, alpha=1.0, resid=None, cossin=None, rot_cols=0, ln_gamma=None, ln_beta=None,
+         ln_eps=1e-5, out16=None, out16_col0=0, ld16=0, out32=None, ld32=0, out32_batch_stride=0,
+         cells=(0, 0)):
+    """C = epilogue(A . W^T) on the tcgen05 path.  `a`/`w` are bf16 tensors; views are expressed with
+    (a_col0, lda) / (b_row0, ldb) so that a column slice of a wider matrix can be an operand."""
+    _require_cuda(a, w, out16, out32)
+    d = GemmDesc()
+    d.a = _ptr(a, a_col0)
+    d.lda = lda
+    d.a_rows = a_rows if a_rows is not None else a.numel() // lda
+    ldb = ldb if ldb is not None else K
+    d.b = _ptr(w, b_row0 * ldb)
+    d.ldb = ldb
+    d.b_rows = b_rows if b_rows is not None else (w.numel() // ldb - b_row0)
+    d.M, d.N, d.K, d.batch = M, N, K, batch
+    d.a_batch_rows, d.b_batch_rows = a_batch_rows, b_batch_rows
+    d.block_n, d.epilogue = block_n, epilogue
+    if conv is not None:
+        d.conv, d.H, d.W, d.Cin = 1, conv[0], conv[1], conv[2]
+    d.bias, d.scale, d.shift = _ptr(bias), _ptr(scale), _ptr(shift)
+    d.relu, d.pool, d.alpha = relu, pool, alpha
+    d.resid, d.cossin, d.rot_cols = _ptr(resid), _ptr(cossin), rot_cols
+    d.ln_gamma, d.ln_beta, d.ln_eps = _ptr(ln_gamma), _ptr(ln_beta), ln_eps
+    d.out16, d.ld16 = _ptr(out16, out16_col0), ld16
+    d.out32, d.ld32, d.out32_batch_stride = _ptr(out32), ld32, out32_batch_stride
+    d.cells_h, d.cells_w = cells
+    _lib.check(_lib.lib().b200_gemm(C.byref(d), _stream()))
+
+
+def make_attn_seqs(entries, device):
+    """entries: iterable of (q_row0, q_len, kv_row0, kv_len[, q_slot, kv_slot]) -> device int32 [n, 6]."""
+    rows = [list(e) + [0] * (6 - len(e)) for e in entries]
+    return torch.tensor(rows, dtype=torch.int32).to(device, non_blocking=True)
+
+
+def attention(q, k, v, seqs, *, num_seqs, max_q_len, heads, ldq, ldk, ldv, q_col0, k_col0, v_col0, scale,
+              out, ld_out, out_col0=0, len_override=None):
+    _require_cuda(q, k, v, seqs, out)
+    d = AttnDesc()
+    d.q, d.q_rows, d.ldq, d.q_col0 = _ptr(q), q.numel() // ldq, ldq, q_col0
+    d.k, d.k_rows, d.ldk, d.k_col0 = _ptr(k), k.numel() // ldk, ldk, k_col0
+    d.v, d.v_rows, d.ldv, d.v_col0 = _ptr(v), v.numel() // ldv, ldv, v_col0
+    d.seqs, d.num_seqs, d.max_q_len, d.heads = _ptr(seqs), num_seqs, max_q_len, heads
+    d.len_override = _ptr(len_override)
+    d.scale = scale
+    d.out, d.ld_out, d.out_col0 = _ptr(out), ld_out, out_col0
+    _lib.check(_lib.lib().b200_attention(C.byref(d), _stream()))
+
+
+# ---- SuperPoint-open ----------------------------------------------------------------------------
+def sp_conv1a(image, w, bias, scale, shift, out):
+    _require_cuda(image, out)
+    b, c, h, wd = image.shape
+    _lib.check(_lib.lib().b200_sp_conv1a(_ptr(image), b, c, h, wd, _ptr(w), _ptr(bias), _ptr(scale), _ptr(shift),
+                                         _ptr(out), _stream()))
+
+
+def sp_nms_border(scores, radius, pad):
+    _require_cuda(scores)
+    b, h, w = scores.shape
+    out = torch.empty_like(scores)
+    _lib.check(_lib.lib().b200_sp_nms_border(_ptr(scores), b, h, w, int(radius), int(pad or 0), _ptr(out), _stream()))
+    return out
+
+
+def sp_count_candidates(nms_map, threshold):
+    b, h, w = nms_map.shape
+    counts = torch.empty(b, dtype=torch.int32, device=nms_map.device)
+    _lib.check(_lib.lib().b200_sp_count_candidates(_ptr(nms_map), b, h, w, float(threshold), _ptr(counts), _stream()))
+    return counts
+
+
+def sp_select_topk(nms_map, threshold, k):
+    _require_cuda(nms_map)
+    b, h, w = nms_map.shape
+    dev = nms_map.device
+    kpts = torch.empty(b, k, 2, dtype=torch.float32, device=dev)
+    scores = torch.empty(b, k, dtype=torch.float32, device=dev)
+    idx = torch.empty(b, k, dtype=torch.int32, device=dev)
+    counts = torch.empty(b, dtype=torch.int32, device=dev)
+    _lib.check(_lib.lib().b200_sp_select_topk(_ptr(nms_map), b, h, w, float(threshold), int(k), _ptr(kpts),
+                                              _ptr(scores), _ptr(idx), _ptr(counts), _stream()))
+    return kpts, scores, idx, counts
+
+
+def sp_sample_descriptors(dense_nhwc, keypoints, stride=8):
+    _require_cuda(dense_nhwc, keypoints)
+    b, hc, wc, c = dense_nhwc.shape
+    k = keypoints.shape[1]
+    out = torch.empty(b, k, c, dtype=torch.float32, device=dense_nhwc.device)
+    _lib.check(_lib.lib().b200_sp_sample_descriptors(_ptr(dense_nhwc), b, hc, wc, c, _ptr(keypoints), k, int(stride),
+                                                     _ptr(out), _stream()))
+    return out
+
+
+# ---- LightGlue ----------------------------------------------------------------------------------
+def lg_ingest(desc, x32, xm, ld_xm, row0=0):
+    rows = desc.numel() // 256
+    _lib.check(_lib.lib().b200_lg_ingest(_ptr(desc), rows, _ptr(x32, row0 * 256), _ptr(xm, row0 * ld_xm), ld_xm,
+                                         _stream()))
+
+
+def lg_posenc(kpts, image_size, wr, cossin, row0=0):
+    b, n, _ = kpts.shape
+    scratch = torch.empty(b, 2, dtype=torch.float32, device=kpts.device) if image_size is None else None
+    _lib.check(_lib.lib().b200_lg_posenc(_ptr(kpts), _ptr(image_size), b, n, _ptr(wr), _ptr(scratch),
+                                         _ptr(cossin, row0 * 64), _stream()))
+
+
+def lg_rowdot(x32, rows, w, bias, out, sigmoid=False, row0=0):
+    _lib.check(_lib.lib().b200_lg_rowdot(_ptr(x32, row0 * 256), rows, _ptr(w), _ptr(bias), int(sigmoid),
+                                         _ptr(out, row0), _stream()))
+
+
+def lg_assignment(sim, z0, z1, threshold):
+    b, m, n = sim.shape
+    dev = sim.device
+    ws = torch.empty(_lib.lib().b200_lg_assignment_workspace(b, m, n), dtype=torch.uint8, device=dev)
+    scores = torch.empty(b, m + 1, n + 1, dtype=torch.float32, device=dev)
+    m0 = torch.empty(b, m, dtype=torch.int64, device=dev)
+    m1 = torch.empty(b, n, dtype=torch.int64, device=dev)
+    ms0 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    ms1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    _lib.check(_lib.lib().b200_lg_assignment(_ptr(sim), _ptr(z0), _ptr(z1), b, m, n, float(threshold), _ptr(ws),
+                                             _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _stream()))
+    return scores, m0, m1, ms0, ms1

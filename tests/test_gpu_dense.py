@@ -1,0 +1,200 @@
+"""GPU parity tests of the dense tcgen05 kernels (GEMM epilogues, implicit-GEMM conv, attention)
+against plain PyTorch fp32 on the same bf16-rounded operands.  Run on the B200 box: pytest -m gpu."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return torch.device("cuda:0")
+
+
+def _rand(shape, dev, seed, scale=1.0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dev)
+
+
+def _bf(t):
+    return t.to(torch.bfloat16)
+
+
+def _close(got, want, rtol, atol, what=""):
+    got, want = got.float(), want.float()
+    err = (got - want).abs()
+    tol = atol + rtol * want.abs()
+    bad = (err > tol).sum().item()
+    assert bad == 0, f"{what}: {bad}/{err.numel()} elements off, max err {err.max().item():.4g}, max ref {want.abs().max().item():.4g}"
+
+
+@pytest.mark.parametrize("M", [128, 300, 4096 + 17])
+def test_linear_bias(dev, M):
+    from glue_factory_b200 import ops
+
+    a, w, b = _bf(_rand((M, 256), dev, 1)), _bf(_rand((256, 256), dev, 2, 1 / 16)), _rand((256,), dev, 3)
+    out = torch.zeros(M, 512, dtype=torch.bfloat16, device=dev)
+    ops.gemm(a, w, M=M, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16, bias=b, out16=out,
+             out16_col0=256, ld16=512)
+    torch.cuda.synchronize()
+    want = a.float() @ w.float().t() + b
+    _close(out[:, 256:], want, 1e-2, 1e-2, "linear")
+    assert out[:, :256].abs().max().item() == 0  # the left half is untouched
+
+
+def test_linear_strided_a_and_n512(dev):
+    from glue_factory_b200 import ops
+
+    M = 777
+    xm = _bf(_rand((M, 512), dev, 4))
+    w, b = _bf(_rand((512, 256), dev, 5, 1 / 16)), _rand((512,), dev, 6)
+    out = torch.zeros(M, 768, dtype=torch.bfloat16, device=dev)
+    ops.gemm(xm, w, M=M, N=512, K=256, lda=512, block_n=256, epilogue=ops.EPI_BIAS_BF16, bias=b, out16=out, ld16=768)
+    torch.cuda.synchronize()
+    want = xm[:, :256].float() @ w.float().t() + b
+    _close(out[:, :512], want, 1e-2, 1e-2, "strided A")
+
+
+def test_qkv_rotary(dev):
+    from glue_factory_b200 import ops
+
+    M = 500
+    a, w, b = _bf(_rand((M, 256), dev, 7)), _bf(_rand((768, 256), dev, 8, 1 / 16)), _rand((768,), dev, 9)
+    ang = _rand((M, 32), dev, 10, 2.0)
+    cs = torch.stack([ang.cos(), ang.sin()], -1).contiguous()
+    out = torch.empty(M, 768, dtype=torch.bfloat16, device=dev)
+    ops.gemm(a, w, M=M, N=768, K=256, lda=256, block_n=256, epilogue=ops.EPI_QKV_ROTARY, bias=b, cossin=cs,
+             rot_cols=512, out16=out, ld16=768)
+    torch.cuda.synchronize()
+    y = a.float() @ w.float().t() + b
+    qk = y[:, :512].view(M, 8, 32, 2)
+    c, s = ang.cos()[:, None, :], ang.sin()[:, None, :]
+    rot = torch.stack([qk[..., 0] * c - qk[..., 1] * s, qk[..., 1] * c + qk[..., 0] * s], -1).reshape(M, 512)
+    _close(out[:, :512], rot, 1e-2, 2e-2, "rotary q,k")
+    _close(out[:, 512:], y[:, 512:], 1e-2, 2e-2, "v")
+
+
+def test_ffn_layernorm_gelu_and_residual(dev):
+    from glue_factory_b200 import ops
+
+    M = 391
+    xm = _bf(_rand((M, 512), dev, 11))
+    w1, b1 = _bf(_rand((512, 512), dev, 12, 1 / 22)), _rand((512,), dev, 13, 0.1)
+    g, be = 1 + _rand((512,), dev, 14, 0.1), _rand((512,), dev, 15, 0.1)
+    h = torch.empty(M, 512, dtype=torch.bfloat16, device=dev)
+    ops.gemm(xm, w1, M=M, N=512, K=512, lda=512, block_n=512, epilogue=ops.EPI_LN_GELU, bias=b1, ln_gamma=g,
+             ln_beta=be, ln_eps=1e-5, out16=h, ld16=512)
+    torch.cuda.synchronize()
+    want = F.gelu(F.layer_norm(xm.float() @ w1.float().t() + b1, (512,), g, be, 1e-5))
+    _close(h, want, 1e-2, 2e-2, "LN+GELU")
+
+    w2, b2 = _bf(_rand((256, 512), dev, 16, 1 / 22)), _rand((256,), dev, 17, 0.1)
+    x32 = _rand((M, 256), dev, 18)
+    x_before = x32.clone()
+    xm2 = torch.zeros(M, 512, dtype=torch.bfloat16, device=dev)
+    ops.gemm(h, w2, M=M, N=256, K=512, lda=512, block_n=256, epilogue=ops.EPI_RESID, bias=b2, resid=x32, out32=x32,
+             ld32=256, out16=xm2, ld16=512)
+    torch.cuda.synchronize()
+    want = x_before + h.float() @ w2.float().t() + b2
+    _close(x32, want, 1e-4, 1e-4, "residual fp32")
+    _close(xm2[:, :256], want, 1e-2, 1e-2, "residual bf16 copy")
+
+
+@pytest.mark.parametrize("B,M,N", [(1, 128, 256), (3, 200, 333), (2, 96, 80)])
+def test_similarity_batched(dev, B, M, N):
+    from glue_factory_b200 import ops
+
+    md = _bf(_rand((B * (M + N), 256), dev, 19, 0.5))
+    sim = torch.full((B, M, N), float("nan"), device=dev)
+    ops.gemm(md, md, M=M, N=N, K=256, lda=256, ldb=256, a_rows=B * (M + N), b_row0=B * M, b_rows=B * N, batch=B,
+             a_batch_rows=M, b_batch_rows=N, block_n=256 if N > 128 else 128, epilogue=ops.EPI_F32, alpha=1.0,
+             out32=sim, ld32=N, out32_batch_stride=M * N)
+    torch.cuda.synchronize()
+    a = md[: B * M].float().view(B, M, 256)
+    b = md[B * M:].float().view(B, N, 256)
+    _close(sim, a @ b.transpose(1, 2), 1e-4, 1e-3, "similarity")
+
+
+@pytest.mark.parametrize("cin,cout,H,W,pool", [(64, 64, 40, 48, 1), (64, 64, 37, 53, 0), (64, 128, 24, 40, 0),
+                                               (128, 128, 19, 21, 1), (128, 512, 16, 24, 0)])
+def test_conv3x3_relu_bn_pool(dev, cin, cout, H, W, pool):
+    from glue_factory_b200 import ops
+
+    B = 2
+    x = _bf(_rand((B, H, W, cin), dev, 20))
+    w = _rand((cout, cin, 3, 3), dev, 21, 1 / math.sqrt(9 * cin))
+    wp = _bf(w.permute(0, 2, 3, 1).reshape(cout, -1)).contiguous()
+    bias, scale, shift = _rand((cout,), dev, 22, 0.1), 1 + _rand((cout,), dev, 23, 0.2), _rand((cout,), dev, 24, 0.2)
+    oh, ow = (H // 2, W // 2) if pool else (H, W)
+    y = torch.zeros(B, oh, ow, cout, dtype=torch.bfloat16, device=dev)
+    ops.gemm(x, wp, M=0, N=cout, K=9 * cin, lda=cin, block_n=min(cout, 256), epilogue=ops.EPI_CONV_RELU_BN, batch=B,
+             conv=(H, W, cin), bias=bias, scale=scale, shift=shift, relu=1, pool=pool, out16=y, ld16=cout)
+    torch.cuda.synchronize()
+    w_r = wp.float().view(cout, 3, 3, cin).permute(0, 3, 1, 2)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w_r, bias, padding=1)
+    ref = F.relu(ref) * scale[None, :, None, None] + shift[None, :, None, None]
+    if pool:
+        ref = F.max_pool2d(ref, 2, 2)
+    _close(y.permute(0, 3, 1, 2), ref, 1e-2, 2e-2, "conv")
+
+
+def test_heads_desc_l2_and_score_softmax(dev):
+    from glue_factory_b200 import ops
+
+    B, h, w = 2, 12, 20
+    cells = B * h * w
+    heads = _bf(_rand((cells, 512), dev, 25))
+    wd, bd = _bf(_rand((256, 256), dev, 26, 1 / 16)), _rand((256,), dev, 27, 0.1)
+    sd, td = 1 + _rand((256,), dev, 28, 0.1), _rand((256,), dev, 29, 0.1)
+    dense = torch.empty(B, h, w, 256, device=dev)
+    ops.gemm(heads, wd, M=cells, N=256, K=256, lda=512, a_col0=256, block_n=256, epilogue=ops.EPI_CONV_BN_L2,
+             bias=bd, scale=sd, shift=td, out32=dense, ld32=256)
+    ws, bs = _bf(_rand((65, 256), dev, 30, 1 / 8)), _rand((65,), dev, 31, 0.1)
+    ss, ts = 1 + _rand((65,), dev, 32, 0.1), _rand((65,), dev, 33, 0.1)
+    heat = torch.empty(B, h * 8, w * 8, device=dev)
+    ops.gemm(heads, ws, M=cells, N=65, K=256, lda=512, a_col0=0, block_n=80, epilogue=ops.EPI_CONV_BN_SOFTMAX_D2S,
+             bias=bs, scale=ss, shift=ts, out32=heat, cells=(h, w))
+    torch.cuda.synchronize()
+    ref_d = F.normalize((heads[:, 256:].float() @ wd.float().t() + bd) * sd + td, dim=1)
+    _close(dense.view(cells, 256), ref_d, 1e-4, 1e-5, "descriptor head")
+    logits = (heads[:, :256].float() @ ws.float().t() + bs) * ss + ts
+    prob = torch.softmax(logits, 1)[:, :64].view(B, h, w, 8, 8).permute(0, 1, 3, 2, 4).reshape(B, h * 8, w * 8)
+    _close(heat, prob, 1e-4, 1e-7, "score head")
+
+
+def _attn_ref(q, k, v, scale):
+    s = (q.float() @ k.float().t()) * scale
+    return torch.softmax(s, -1) @ v.float()
+
+
+@pytest.mark.parametrize("lens", [[(128, 128)], [(200, 333), (77, 130)], [(2048, 2048)]])
+def test_attention(dev, lens):
+    from glue_factory_b200 import ops
+
+    H = 4
+    total_q = sum(a for a, _ in lens)
+    total_kv = sum(b for _, b in lens)
+    qb = _bf(_rand((total_q, 768), dev, 34))
+    kvb = _bf(_rand((total_kv, 768), dev, 35))
+    entries, qo, ko = [], 0, 0
+    for a, b in lens:
+        entries.append((qo, a, ko, b))
+        qo += a
+        ko += b
+    seqs = ops.make_attn_seqs(entries, dev)
+    out = torch.zeros(total_q, 256, dtype=torch.bfloat16, device=dev)
+    ops.attention(qb, kvb, kvb, seqs, num_seqs=len(lens), max_q_len=max(a for a, _ in lens), heads=H, ldq=768,
+                  ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=out, ld_out=256)
+    torch.cuda.synchronize()
+    for (q0, ql, k0, kl) in entries:
+        for hd in range(H):
+            ref = _attn_ref(qb[q0:q0 + ql, hd * 64:(hd + 1) * 64], kvb[k0:k0 + kl, 256 + hd * 64:256 + (hd + 1) * 64],
+                            kvb[k0:k0 + kl, 512 + hd * 64:512 + (hd + 1) * 64], 0.125)
+            _close(out[q0:q0 + ql, hd * 64:(hd + 1) * 64], ref, 2e-2, 2e-2, f"attention head {hd}")
