@@ -79,7 +79,7 @@ def _lg_inputs(seed, B, M, N):
     k0 = (g.random((B, M, 2)) * size[:, None]).astype(np.float32)
     k1 = (g.random((B, N, 2)) * size[:, None]).astype(np.float32)
     d0 = g.standard_normal((B, M, 256)).astype(np.float32)
-    d1 = np.stack([d0[b][g.permutation(M)[:N] % M] for b in range(B)]) + 0.35 * g.standard_normal((B, N, 256)).astype(np.float32)
+    d1 = np.stack([d0[b][g.integers(0, M, N)] for b in range(B)]) + 0.35 * g.standard_normal((B, N, 256)).astype(np.float32)
     d0 /= np.linalg.norm(d0, axis=-1, keepdims=True)
     d1 /= np.linalg.norm(d1, axis=-1, keepdims=True)
     return [torch.from_numpy(x) for x in (k0, k1, d0, d1.astype(np.float32), size)]
