@@ -1,0 +1,329 @@
+"""Benchmark of the SuperPoint-open + LightGlue forward pass (BASELINE.json configs[1]).
+
+    python bench.py --gpus N --steps K --warmup W            # B200 kernels
+    python bench.py --impl reference --gpus N --steps K ...  # CPU oracle port on the host cores
+
+One step = one pass of the hot path over one batch of 32 synthetic 1024x1024 image pairs at 2048
+keypoints (extractor on both views + matcher, through TwoViewPipeline.forward).  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from glue_factory_b200 import synth  # noqa: E402
+
+METRIC = "SP+LightGlue pairs/s @2048 kpts"
+H = W = 1024
+KPTS = 2048
+PAIRS = 32
+EXTRACTOR_CONF = dict(name="extractors.superpoint_open", max_num_keypoints=KPTS, detection_threshold=-1,
+                      nms_radius=3, force_num_keypoints=False)
+MATCHER_CONF = dict(name="matchers.lightglue", filter_threshold=0.1, flash=False)
+# algorithmic FLOPs per pair: 2 x 177.86 (SuperPoint-open) + 229.8 (LightGlue)
+GFLOP_PER_PAIR = 585.5
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return dict(hbm=p["hbm_gbs"], tf_burst=p["bf16_tflops"], tf_sustained=p["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+def make_pairs(first, count, seed=1234):
+    """`count` synthetic pairs: 8 seeded base pairs, the rest are flips of them (cheap on the host)."""
+    base = min(count, 8)
+    im0, im1, _ = synth.synthetic_batch(first, base, H, W, seed)
+    out0, out1 = [im0], [im1]
+    flips = [(-1,), (-2,), (-1, -2)]
+    i = 0
+    while sum(x.shape[0] for x in out0) < count:
+        out0.append(torch.flip(im0, flips[i % 3]))
+        out1.append(torch.flip(im1, flips[i % 3]))
+        i += 1
+    return torch.cat(out0)[:count].contiguous(), torch.cat(out1)[:count].contiguous()
+
+
+def weight_files():
+    d = tempfile.mkdtemp(prefix="b200glue_w_")
+    sp, lg = os.path.join(d, "sp.pth"), os.path.join(d, "lg.pth")
+    torch.save(synth.superpoint_open_state_dict(), sp)
+    torch.save(synth.lightglue_state_dict(), lg)
+    return sp, lg
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 6 or not parts[0].isdigit():
+                continue
+            sm.append(int(parts[0]))
+            mx = int(parts[1])
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def dist_env():
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    return rank, world, int(os.environ.get("LOCAL_RANK", 0))
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (oracle/ is a torch-CPU fp32 restatement of the reference, pinned against
+# reference-generated vectors; the reference itself cannot travel to the GPU box)
+# ---------------------------------------------------------------------------------------------
+def oracle_pair_fn():
+    from oracle import lightglue as olg
+    from oracle import sp_open as osp
+
+    sp_sd, lg_sd = synth.superpoint_open_state_dict(), synth.lightglue_state_dict()
+    sp_conf = dict(max_num_keypoints=KPTS, detection_threshold=-1, nms_radius=3)
+    size = torch.tensor([[float(W), float(H)]])
+
+    def run(im0, im1):
+        with torch.no_grad():
+            p0 = osp.forward(sp_sd, im0[None], sp_conf)
+            p1 = osp.forward(sp_sd, im1[None], sp_conf)
+            return olg.forward(lg_sd, p0["keypoints"], p1["keypoints"], p0["descriptors"], p1["descriptors"],
+                               size, size, dict(filter_threshold=0.1))
+
+    return run
+
+
+def time_cpu(num_pairs, warmup_pairs):
+    torch.set_num_threads(os.cpu_count() or 1)
+    run = oracle_pair_fn()
+    im0, im1 = make_pairs(0, min(8, max(1, num_pairs)))
+    for i in range(warmup_pairs):
+        run(im0[i % len(im0)], im1[i % len(im0)])
+    t0 = time.perf_counter()
+    for i in range(num_pairs):
+        run(im0[i % len(im0)], im1[i % len(im0)])
+    dt = time.perf_counter() - t0
+    return num_pairs / dt, dt, torch.get_num_threads()
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    steps, warmup = args.steps, args.warmup
+    pps, dt, cores = time_cpu(steps, warmup)
+    sample = f"{steps} timed step(s) of 1 pair each (1024x1024, 2048 kpts, fp32) after {warmup} warm-up pair(s)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": pps, "unit": "pairs/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": 1000.0 * dt / steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: SP-open + LightGlue, 2048 kpts, 1024x1024 synthetic pairs; "
+                               "CPU arm runs 1 pair per step", "pairs_per_step": 1},
+        "cpu_baseline": {"value": pps, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": pps, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+RESULT_KEYS = ["keypoints0", "keypoints1", "keypoint_scores0", "keypoint_scores1", "matches0", "matches1",
+               "matching_scores0", "matching_scores1"]
+
+
+def run_b200(args):
+    import torch.distributed as dist
+
+    from glue_factory_b200 import ops
+    from gluefactory.models import get_model
+
+    rank, world, local = dist_env()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    steps, warmup = args.steps, max(3, args.warmup)
+    sp_path, lg_path = weight_files()
+    pipe = get_model("two_view_pipeline")({
+        "extractor": {**EXTRACTOR_CONF, "weights": sp_path},
+        "matcher": {**MATCHER_CONF, "weights": lg_path},
+    }).to(dev).eval()
+
+    im0, im1 = make_pairs(rank * PAIRS, PAIRS)
+    host = {"image0": im0.pin_memory(), "image1": im1.pin_memory(),
+            "size": torch.tensor([[float(W), float(H)]] * PAIRS).pin_memory()}
+    h2d_bytes = sum(t.numel() * t.element_size() for t in host.values())
+
+    def to_views(i0, i1, size):
+        return {"view0": {"image": i0, "image_size": size}, "view1": {"image": i1, "image_size": size}}
+
+    resident = to_views(host["image0"].to(dev), host["image1"].to(dev), host["size"].to(dev))
+    out_host = {}
+
+    def step_resident():
+        with torch.no_grad():
+            return pipe(resident)
+
+    def step_e2e():
+        with torch.no_grad():
+            pred = pipe(to_views(host["image0"].to(dev, non_blocking=True), host["image1"].to(dev, non_blocking=True),
+                                 host["size"].to(dev, non_blocking=True)))
+        for k in RESULT_KEYS:
+            if k not in out_host:
+                out_host[k] = torch.empty(pred[k].shape, dtype=pred[k].dtype).pin_memory()
+            out_host[k].copy_(pred[k], non_blocking=True)
+        torch.cuda.synchronize()  # the host reads the result record of this step
+        return pred
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, n, profile):
+        barrier()
+        ops.reset_stats(profile=profile)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item()
+
+    for _ in range(warmup):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms = timed(step_resident, steps, profile=True)
+    clocks = sampler.stop()
+    launches = ops.launches()
+    records = ops.profile_records()
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, steps, profile=False)
+    d2h_bytes = sum(t.numel() * t.element_size() for t in out_host.values())
+
+    # final result gather (outside the timed region): fixed-size records per pair
+    gather_ms = None
+    if world > 1:
+        rec = step_resident()["matches0"].to(torch.int32).contiguous()
+        bucket = torch.empty(world * rec.numel(), dtype=torch.int32, device=dev)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        dist.all_gather_into_tensor(bucket, rec.view(-1))
+        torch.cuda.synchronize()
+        gather_ms = 1000.0 * (time.perf_counter() - t0)
+
+    if rank == 0:
+        pk = peaks()
+        per_tag = {}
+        for tag, work, a, b in records:
+            t = per_tag.setdefault(tag, [0.0, 0, 0.0])
+            t[0] += a.elapsed_time(b)
+            t[1] += 1
+            t[2] += work
+        ranked = sorted(per_tag.items(), key=lambda kv: -kv[1][0])
+        top_tag, (top_ms, top_n, top_work) = ranked[0]
+        tensor_bound = top_tag.startswith(("conv3x3", "gemm", "attention"))
+        achieved = top_work / (top_ms * 1e-3) / (1e12 if tensor_bound else 1e9)
+        peak = pk["tf_sustained"] if tensor_bound else pk["hbm"]
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get(top_tag)
+        total_pairs = PAIRS * world * steps
+        value = total_pairs / (ms * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": "pairs/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "configs[1]: SuperPoint-open + LightGlue, 2048 kpts, 1024x1024 synthetic pairs, "
+                                   "batch 32 pairs per GPU per step", "pairs_per_step_per_gpu": PAIRS,
+                       "image": [H, W], "keypoints": KPTS, "extractor": {k: v for k, v in EXTRACTOR_CONF.items()},
+                       "matcher": MATCHER_CONF, "parallelism": f"pairs sharded over {world} GPU(s), no collective in the step",
+                       "l2": "inputs_exceed_l2 (268 MB of images, >10 GB of activations per step)"},
+            "e2e": {"value": total_pairs / (ms_e2e * 1e-3), "unit": "pairs/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": d2h_bytes, "ms_per_step": ms_e2e / steps},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "tensor" if tensor_bound else "hbm", "kernel": top_tag, "achieved": achieved,
+                         "peak": peak, "unit": "TFLOP/s" if tensor_bound else "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": pk["src"] + (" sustained bf16" if tensor_bound else " copy"),
+                         "launches": top_n, "avg_ms": top_ms / top_n, "share_of_step": top_ms / ms},
+            "pipeline": {"tflops": GFLOP_PER_PAIR * value / world / 1e3, "frac_of_sustained_peak":
+                         GFLOP_PER_PAIR * value / world / 1e3 / pk["tf_sustained"]},
+            "kernels": [{"tag": t, "ms_per_step": v[0] / steps, "launches_per_step": v[1] / steps,
+                         "rate": v[2] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None} for t, v in ranked[:12]],
+            "gather_ms": gather_ms,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            pps, dt, cores = time_cpu(2, 1)
+            line["cpu_baseline"] = {"value": pps, "unit": "pairs/s", "cores": cores, "kind": "port",
+                                    "sample": "2 timed pairs after 1 warm-up pair of the same workload (1024x1024, 2048 kpts), "
+                                              "oracle port, fp32"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

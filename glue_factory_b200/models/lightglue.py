@@ -197,13 +197,13 @@ class LightGlue(nn.Module):
         ops.gemm(ws["h"], w2, M=T, N=256, K=512, lda=512, block_n=256, epilogue=ops.EPI_RESID, bias=b2,
                  resid=ws["x32"], out32=ws["x32"], ld32=256, out16=ws["xm"], ld16=512)
 
-    def _layer(self, P, ws, T, seqs_self, seqs_cross, nseq, max_len):
+    def _layer(self, P, ws, T, seqs_self, seqs_cross, nseq, max_len, work_self=0.0, work_cross=0.0):
         # self attention (lightglue.py:144-157)
         ops.gemm(ws["xm"], P["wqkv"], M=T, N=768, K=256, lda=512, block_n=256, epilogue=ops.EPI_QKV_ROTARY,
                  bias=P["bqkv"], cossin=ws["cs"], rot_cols=512, out16=ws["qkv"], ld16=768)
         ops.attention(ws["qkv"], ws["qkv"], ws["qkv"], seqs_self, num_seqs=nseq, max_q_len=max_len, heads=4,
                       ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=ws["ctx"],
-                      ld_out=256)
+                      ld_out=256, attn_work=work_self)
         ops.gemm(ws["ctx"], P["wo"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
                  bias=P["bo"], out16=ws["xm"], out16_col0=256, ld16=512)
         self._ffn_block(ws, T, P["s_w1"], P["s_b1"], P["s_g"], P["s_be"], P["s_eps"], P["s_w2"], P["s_b2"])
@@ -212,7 +212,7 @@ class LightGlue(nn.Module):
                  bias=P["bc"], out16=ws["qkv"], ld16=768)
         ops.attention(ws["qkv"], ws["qkv"], ws["qkv"], seqs_cross, num_seqs=nseq, max_q_len=max_len, heads=4,
                       ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=0, v_col0=256, scale=0.125, out=ws["ctx"],
-                      ld_out=256)
+                      ld_out=256, attn_work=work_cross)
         ops.gemm(ws["ctx"], P["wco"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
                  bias=P["bco"], out16=ws["xm"], out16_col0=256, ld16=512)
         self._ffn_block(ws, T, P["c_w1"], P["c_b1"], P["c_g"], P["c_be"], P["c_eps"], P["c_w2"], P["c_b2"])
@@ -279,7 +279,9 @@ class LightGlue(nn.Module):
         seqs_cross = ops.make_attn_seqs(
             [(b * M, M, off1 + b * N, N) for b in range(B)] + [(off1 + b * N, N, b * M, M) for b in range(B)], dev)
         for i in range(self.conf.n_layers):
-            self._layer(P["layers"][i], ws, T, seqs_self, seqs_cross, 2 * B, max(M, N))
+            # algorithmic FLOPs: self 1024 n^2 per image, cross 1536 M N per pair (sim counted once)
+            self._layer(P["layers"][i], ws, T, seqs_self, seqs_cross, 2 * B, max(M, N),
+                        work_self=1024.0 * B * (M * M + N * N), work_cross=1536.0 * B * M * N)
         scores, m0, m1, ms0, ms1, _ = self._assign(P["assign"][self.conf.n_layers - 1], ws, B, M, N, T)
         x = ws["x32"]
         return {

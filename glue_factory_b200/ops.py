@@ -20,6 +20,45 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+# ---- launch accounting (bench.py): number of kernels launched, optional CUDA-event timing per tag --
+class _Stats:
+    launches = 0
+    profile = None  # None, or a list collecting (tag, work, start_event, end_event)
+
+
+def reset_stats(profile=False):
+    _Stats.launches = 0
+    _Stats.profile = [] if profile else None
+
+
+def launches():
+    return _Stats.launches
+
+
+def profile_records():
+    return _Stats.profile or []
+
+
+class _timed:
+    """Counts `n` kernel launches; when profiling, brackets them with CUDA events on the current stream."""
+
+    def __init__(self, tag, n=1, work=0.0):
+        self.tag, self.n, self.work = tag, n, work
+
+    def __enter__(self):
+        _Stats.launches += self.n
+        if _Stats.profile is not None:
+            self.t0 = torch.cuda.Event(enable_timing=True)
+            self.t1 = torch.cuda.Event(enable_timing=True)
+            self.t0.record()
+
+    def __exit__(self, *exc):
+        if _Stats.profile is not None:
+            self.t1.record()
+            _Stats.profile.append((self.tag, self.work, self.t0, self.t1))
+        return False
+
+
 def _ptr(t, offset_elems: int = 0):
     if t is None:
         return None
@@ -60,7 +99,12 @@ def gemm(a, w, *, M, N, K, lda, block_n, epilogue, a_rows=None, a_col0=0, ldb=No
     d.out16, d.ld16 = _ptr(out16, out16_col0), ld16
     d.out32, d.ld32, d.out32_batch_stride = _ptr(out32), ld32, out32_batch_stride
     d.cells_h, d.cells_w = cells
-    _lib.check(_lib.lib().b200_gemm(C.byref(d), _stream()))
+    if conv is not None:
+        tag, work = f"conv3x3_{conv[2]}to{N}", 2.0 * batch * conv[0] * conv[1] * N * K
+    else:
+        tag, work = f"gemm_epi{epilogue}_n{N}_k{K}", 2.0 * batch * M * N * K
+    with _timed(tag, 1, work):
+        _lib.check(_lib.lib().b200_gemm(C.byref(d), _stream()))
 
 
 def make_attn_seqs(entries, device):
@@ -70,7 +114,7 @@ def make_attn_seqs(entries, device):
 
 
 def attention(q, k, v, seqs, *, num_seqs, max_q_len, heads, ldq, ldk, ldv, q_col0, k_col0, v_col0, scale,
-              out, ld_out, out_col0=0, len_override=None):
+              out, ld_out, out_col0=0, len_override=None, attn_work=0.0):
     _require_cuda(q, k, v, seqs, out)
     d = AttnDesc()
     d.q, d.q_rows, d.ldq, d.q_col0 = _ptr(q), q.numel() // ldq, ldq, q_col0
@@ -80,29 +124,33 @@ def attention(q, k, v, seqs, *, num_seqs, max_q_len, heads, ldq, ldk, ldv, q_col
     d.len_override = _ptr(len_override)
     d.scale = scale
     d.out, d.ld_out, d.out_col0 = _ptr(out), ld_out, out_col0
-    _lib.check(_lib.lib().b200_attention(C.byref(d), _stream()))
+    with _timed("attention", 1, attn_work):
+        _lib.check(_lib.lib().b200_attention(C.byref(d), _stream()))
 
 
 # ---- SuperPoint-open ----------------------------------------------------------------------------
 def sp_conv1a(image, w, bias, scale, shift, out):
     _require_cuda(image, out)
     b, c, h, wd = image.shape
-    _lib.check(_lib.lib().b200_sp_conv1a(_ptr(image), b, c, h, wd, _ptr(w), _ptr(bias), _ptr(scale), _ptr(shift),
-                                         _ptr(out), _stream()))
+    with _timed("sp_conv1a", 1, 2.0 * b * h * wd * 64 * 9):
+        _lib.check(_lib.lib().b200_sp_conv1a(_ptr(image), b, c, h, wd, _ptr(w), _ptr(bias), _ptr(scale), _ptr(shift),
+                                             _ptr(out), _stream()))
 
 
 def sp_nms_border(scores, radius, pad):
     _require_cuda(scores)
     b, h, w = scores.shape
     out = torch.empty_like(scores)
-    _lib.check(_lib.lib().b200_sp_nms_border(_ptr(scores), b, h, w, int(radius), int(pad or 0), _ptr(out), _stream()))
+    with _timed("sp_nms_border", 1, 8.0 * b * h * w):
+        _lib.check(_lib.lib().b200_sp_nms_border(_ptr(scores), b, h, w, int(radius), int(pad or 0), _ptr(out), _stream()))
     return out
 
 
 def sp_count_candidates(nms_map, threshold):
     b, h, w = nms_map.shape
     counts = torch.empty(b, dtype=torch.int32, device=nms_map.device)
-    _lib.check(_lib.lib().b200_sp_count_candidates(_ptr(nms_map), b, h, w, float(threshold), _ptr(counts), _stream()))
+    with _timed("sp_count", 1, 0.0):
+        _lib.check(_lib.lib().b200_sp_count_candidates(_ptr(nms_map), b, h, w, float(threshold), _ptr(counts), _stream()))
     return counts
 
 
@@ -114,8 +162,9 @@ def sp_select_topk(nms_map, threshold, k):
     scores = torch.empty(b, k, dtype=torch.float32, device=dev)
     idx = torch.empty(b, k, dtype=torch.int32, device=dev)
     counts = torch.empty(b, dtype=torch.int32, device=dev)
-    _lib.check(_lib.lib().b200_sp_select_topk(_ptr(nms_map), b, h, w, float(threshold), int(k), _ptr(kpts),
-                                              _ptr(scores), _ptr(idx), _ptr(counts), _stream()))
+    with _timed("sp_select_topk", 1, 4.0 * b * h * w):
+        _lib.check(_lib.lib().b200_sp_select_topk(_ptr(nms_map), b, h, w, float(threshold), int(k), _ptr(kpts),
+                                                  _ptr(scores), _ptr(idx), _ptr(counts), _stream()))
     return kpts, scores, idx, counts
 
 
@@ -124,28 +173,32 @@ def sp_sample_descriptors(dense_nhwc, keypoints, stride=8):
     b, hc, wc, c = dense_nhwc.shape
     k = keypoints.shape[1]
     out = torch.empty(b, k, c, dtype=torch.float32, device=dense_nhwc.device)
-    _lib.check(_lib.lib().b200_sp_sample_descriptors(_ptr(dense_nhwc), b, hc, wc, c, _ptr(keypoints), k, int(stride),
-                                                     _ptr(out), _stream()))
+    with _timed("sp_sample_desc", 1, b * k * c * 4 * 5.0):
+        _lib.check(_lib.lib().b200_sp_sample_descriptors(_ptr(dense_nhwc), b, hc, wc, c, _ptr(keypoints), k, int(stride),
+                                                         _ptr(out), _stream()))
     return out
 
 
 # ---- LightGlue ----------------------------------------------------------------------------------
 def lg_ingest(desc, x32, xm, ld_xm, row0=0):
     rows = desc.numel() // 256
-    _lib.check(_lib.lib().b200_lg_ingest(_ptr(desc), rows, _ptr(x32, row0 * 256), _ptr(xm, row0 * ld_xm), ld_xm,
-                                         _stream()))
+    with _timed("lg_ingest", 1, rows * 256 * 10.0):
+        _lib.check(_lib.lib().b200_lg_ingest(_ptr(desc), rows, _ptr(x32, row0 * 256), _ptr(xm, row0 * ld_xm), ld_xm,
+                                             _stream()))
 
 
 def lg_posenc(kpts, image_size, wr, cossin, row0=0):
     b, n, _ = kpts.shape
     scratch = torch.empty(b, 2, dtype=torch.float32, device=kpts.device) if image_size is None else None
-    _lib.check(_lib.lib().b200_lg_posenc(_ptr(kpts), _ptr(image_size), b, n, _ptr(wr), _ptr(scratch),
-                                         _ptr(cossin, row0 * 64), _stream()))
+    with _timed("lg_posenc", 1 if image_size is not None else 2, b * n * 264.0):
+        _lib.check(_lib.lib().b200_lg_posenc(_ptr(kpts), _ptr(image_size), b, n, _ptr(wr), _ptr(scratch),
+                                             _ptr(cossin, row0 * 64), _stream()))
 
 
 def lg_rowdot(x32, rows, w, bias, out, sigmoid=False, row0=0):
-    _lib.check(_lib.lib().b200_lg_rowdot(_ptr(x32, row0 * 256), rows, _ptr(w), _ptr(bias), int(sigmoid),
-                                         _ptr(out, row0), _stream()))
+    with _timed("lg_rowdot", 1, rows * 1028.0):
+        _lib.check(_lib.lib().b200_lg_rowdot(_ptr(x32, row0 * 256), rows, _ptr(w), _ptr(bias), int(sigmoid),
+                                             _ptr(out, row0), _stream()))
 
 
 def lg_assignment(sim, z0, z1, threshold):
@@ -157,6 +210,7 @@ def lg_assignment(sim, z0, z1, threshold):
     m1 = torch.empty(b, n, dtype=torch.int64, device=dev)
     ms0 = torch.empty(b, m, dtype=torch.float32, device=dev)
     ms1 = torch.empty(b, n, dtype=torch.float32, device=dev)
-    _lib.check(_lib.lib().b200_lg_assignment(_ptr(sim), _ptr(z0), _ptr(z1), b, m, n, float(threshold), _ptr(ws),
-                                             _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _stream()))
+    with _timed("lg_assignment", 5, 12.0 * b * m * n):
+        _lib.check(_lib.lib().b200_lg_assignment(_ptr(sim), _ptr(z0), _ptr(z1), b, m, n, float(threshold), _ptr(ws),
+                                                 _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _stream()))
     return scores, m0, m1, ms0, ms1
