@@ -242,7 +242,8 @@ def run_b200(args):
     ms = timed(step_resident, steps, profile=True)
     clocks = sampler.stop()
     launches = ops.launches()
-    records = ops.profile_records()
+    records = list(ops.profile_records())
+    ops.reset_stats(profile=False)
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, steps, profile=False)
@@ -294,7 +295,7 @@ def run_b200(args):
             "roofline": {"bound": "tensor" if tensor_bound else "hbm", "kernel": top_tag, "achieved": achieved,
                          "peak": peak, "unit": "TFLOP/s" if tensor_bound else "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": pk["src"] + (" sustained bf16" if tensor_bound else " copy"),
-                         "launches": top_n, "avg_ms": top_ms / top_n, "share_of_step": top_ms / ms},
+                         "launches_in_timed_region": top_n, "avg_ms": top_ms / top_n, "share_of_step": top_ms / ms},
             "pipeline": {"tflops": GFLOP_PER_PAIR * value / world / 1e3, "frac_of_sustained_peak":
                          GFLOP_PER_PAIR * value / world / 1e3 / pk["tf_sustained"]},
             "kernels": [{"tag": t, "ms_per_step": v[0] / steps, "launches_per_step": v[1] / steps,
