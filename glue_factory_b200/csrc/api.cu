@@ -263,4 +263,22 @@ int b200_lg_assignment(const float* sim, const float* z0, const float* z1, int B
                              mscores1, static_cast<cudaStream_t>(stream));
 }
 
+int b200_lg_count_below(const float* conf, int n, float threshold, int* out, b200_stream_t stream) {
+    return launch_count_below(conf, n, threshold, out, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_prune(const float* match, const float* conf, int n0, int n1, float match_thr, float conf_thr,
+                  int* pos_scratch, int* counts, const float* x_src, float* x_dst, const void* xm_src, void* xm_dst,
+                  long long ld_xm, const void* cs_src, void* cs_dst, const int* ind_src, int* ind_dst,
+                  long long* prune0, long long* prune1, b200_stream_t stream) {
+    B200_REQUIRE(n0 >= 0 && n1 >= 0 && match && pos_scratch && counts, "prune: bad arguments");
+    return launch_prune(match, conf, n0, n1, match_thr, conf_thr, pos_scratch, counts, x_src, x_dst, xm_src, xm_dst,
+                        ld_xm, cs_src, cs_dst, ind_src, ind_dst, prune0, prune1, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_scatter_matches(const long long* m0, const long long* m1, const float* ms0, const float* ms1,
+                            const int* ind, int n0, int n1, long long* out_m0, long long* out_m1, float* out_ms0,
+                            float* out_ms1, b200_stream_t stream) {
+    return launch_scatter_matches(m0, m1, ms0, ms1, ind, n0, n1, out_m0, out_m1, out_ms0, out_ms1,
+                                  static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

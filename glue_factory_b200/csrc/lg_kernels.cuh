@@ -13,4 +13,12 @@ size_t assignment_workspace_bytes(int B, int M, int N);
 int launch_assignment(const float* sim, const float* z0, const float* z1, int B, int M, int N, float threshold,
                       void* workspace, float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
                       cudaStream_t stream);
+int launch_count_below(const float* conf, int n, float thr, int* out, cudaStream_t stream);
+int launch_prune(const float* match, const float* conf, int n0, int n1, float match_thr, float conf_thr, int* pos,
+                 int* counts, const float* x_src, float* x_dst, const void* xm_src, void* xm_dst, long long ld_xm,
+                 const void* cs_src, void* cs_dst, const int* ind_src, int* ind_dst, long long* prune0,
+                 long long* prune1, cudaStream_t stream);
+int launch_scatter_matches(const long long* m0, const long long* m1, const float* ms0, const float* ms1, const int* ind,
+                           int n0, int n1, long long* out_m0, long long* out_m1, float* out_ms0, float* out_ms1,
+                           cudaStream_t stream);
 }  // namespace b200

@@ -214,3 +214,24 @@ def lg_assignment(sim, z0, z1, threshold):
         _lib.check(_lib.lib().b200_lg_assignment(_ptr(sim), _ptr(z0), _ptr(z1), b, m, n, float(threshold), _ptr(ws),
                                                  _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _stream()))
     return scores, m0, m1, ms0, ms1
+
+
+# ---- adaptive depth / width ---------------------------------------------------------------------
+def lg_count_below(conf, n, threshold, out):
+    with _timed("lg_count_below", 1, n * 4.0):
+        _lib.check(_lib.lib().b200_lg_count_below(_ptr(conf), int(n), float(threshold), _ptr(out), _stream()))
+
+
+def lg_prune(match, conf, n0, n1, match_thr, conf_thr, pos, counts, src, dst, ind_src, ind_dst, prune0, prune1):
+    """src / dst: dicts with x32, xm, cs (see LightGlue._workspace)."""
+    with _timed("lg_prune", 2, (n0 + n1) * 3600.0):
+        _lib.check(_lib.lib().b200_lg_prune(_ptr(match), _ptr(conf), int(n0), int(n1), float(match_thr), float(conf_thr),
+                                            _ptr(pos), _ptr(counts), _ptr(src["x32"]), _ptr(dst["x32"]), _ptr(src["xm"]),
+                                            _ptr(dst["xm"]), 512, _ptr(src["cs"]), _ptr(dst["cs"]), _ptr(ind_src),
+                                            _ptr(ind_dst), _ptr(prune0), _ptr(prune1), _stream()))
+
+
+def lg_scatter_matches(m0, m1, ms0, ms1, ind, n0, n1, out_m0, out_m1, out_ms0, out_ms1):
+    with _timed("lg_scatter_matches", 1, (n0 + n1) * 40.0):
+        _lib.check(_lib.lib().b200_lg_scatter_matches(_ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ind), int(n0), int(n1),
+                                                      _ptr(out_m0), _ptr(out_m1), _ptr(out_ms0), _ptr(out_ms1), _stream()))

@@ -138,6 +138,24 @@ int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, 
                        float* scores /*[B,M+1,N+1]*/, long long* matches0, long long* matches1,
                        float* mscores0, float* mscores1, b200_stream_t stream);
 
+
+/* ---- adaptive depth / width (batch size 1; lightglue.py:470-511,527-552) ---------------------- */
+/* check_if_stop: *out = number of entries of conf[0..n) below `threshold` (out is zeroed first) */
+int b200_lg_count_below(const float* conf, int n, float threshold, int* out, b200_stream_t stream);
+/* get_pruning_mask + index_select compaction: keep = match > match_thr OR (conf != NULL AND conf <= conf_thr).
+ * Tokens are rows [0,n0) (image 0) and [n0,n0+n1) (image 1) of x_src (fp32 [.,256]), xm_src (bf16, ld_xm),
+ * cs_src (float2 [.,32]) and ind_src (original indices).  Kept rows are packed, order preserved, image 1
+ * right behind image 0, into the *_dst buffers; counts[0..1] = kept per image; prune{0,1}[orig] += 1. */
+int b200_lg_prune(const float* match, const float* conf, int n0, int n1, float match_thr, float conf_thr,
+                  int* pos_scratch /*[n0+n1]*/, int* counts /*[2]*/, const float* x_src, float* x_dst,
+                  const void* xm_src, void* xm_dst, long long ld_xm, const void* cs_src, void* cs_dst,
+                  const int* ind_src, int* ind_dst, long long* prune0, long long* prune1, b200_stream_t stream);
+/* scatter matches of the pruned problem back to original keypoint indices (lightglue.py:499-509);
+ * the outputs must be pre-filled with -1 / 0 */
+int b200_lg_scatter_matches(const long long* m0, const long long* m1, const float* ms0, const float* ms1,
+                            const int* ind /*[n0+n1]*/, int n0, int n1, long long* out_m0, long long* out_m1,
+                            float* out_ms0, float* out_ms1, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -139,3 +139,33 @@ def test_pipeline_boat_vs_reference_golden(dev, golden_dir, weight_files):
         want = {tuple(p) for p in g[f"keypoints{i}"][0].tolist()}
         print(f"view{i}: keypoint set overlap with the reference {len(got & want) / 1024:.4f}")
         assert len(got & want) / 1024 > 0.85  # bf16 conv stack moves borderline detections
+
+
+@pytest.mark.parametrize("name", ["lg_adaptive", "lg_prune_only", "lg_depth_only"])
+def test_lightglue_adaptive_vs_reference_golden(dev, golden_dir, weight_files, name):
+    """Configuration 3 semantics (early exit + point pruning) against vectors of the patched reference."""
+    from gluefactory.models import get_model
+
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    model = get_model("matchers.lightglue")({
+        "weights": weight_files[1], "filter_threshold": 0.1, "depth_confidence": float(g["depth_confidence"]),
+        "width_confidence": float(g["width_confidence"])}).to(dev).eval()
+    size = torch.from_numpy(g["image_size"]).to(dev)
+    data = {"keypoints0": torch.from_numpy(g["keypoints0"]).to(dev), "keypoints1": torch.from_numpy(g["keypoints1"]).to(dev),
+            "descriptors0": torch.from_numpy(g["descriptors0"]).to(dev), "descriptors1": torch.from_numpy(g["descriptors1"]).to(dev),
+            "view0": {"image_size": size}, "view1": {"image_size": size}}
+    with torch.no_grad():
+        pred = model(data)
+    # same exit layer and the same surviving keypoints as the reference
+    assert tuple(pred["log_assignment"].shape) == g["log_assignment"].shape
+    assert pred["prune0"].dtype == torch.from_numpy(g["prune0"]).dtype
+    np.testing.assert_array_equal(pred["prune0"].cpu().numpy(), g["prune0"])
+    np.testing.assert_array_equal(pred["prune1"].cpu().numpy(), g["prune1"])
+    agree = (pred["matches0"].cpu().numpy() == g["matches0"]).mean()
+    print(name, "match agreement", agree, "log_assignment", g["log_assignment"].shape)
+    assert agree >= 0.98
+    rel = np.abs(pred["log_assignment"].cpu().numpy() - g["log_assignment"]) / np.maximum(np.abs(g["log_assignment"]), 1e-3)
+    assert np.median(rel) < 2e-2
+    rd = pred["ref_descriptors0"].cpu().numpy()
+    assert rd.shape == g["ref_descriptors0"].shape
+    assert np.linalg.norm(rd - g["ref_descriptors0"]) / np.linalg.norm(g["ref_descriptors0"]) < 3e-2
