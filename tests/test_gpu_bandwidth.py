@@ -147,3 +147,60 @@ def test_log_assignment_and_filter(dev, B, M, N):
     np.testing.assert_allclose(ms0.cpu().numpy(), ws0.numpy(), rtol=1e-5)
     np.testing.assert_allclose(ms1.cpu().numpy(), ws1.numpy(), rtol=1e-5)
     assert m0.dtype == torch.int64
+
+
+@pytest.mark.parametrize("n0,n1,with_conf", [(160, 160, True), (1500, 2300, True), (1024, 1, False), (33, 4096, False)])
+def test_prune_compaction_bit_exact(dev, n0, n1, with_conf):
+    """get_pruning_mask + index_select compaction + prune counters + scatter back (lightglue.py:478-511)."""
+    from glue_factory_b200 import ops
+
+    g = torch.Generator().manual_seed(n0 + n1)
+    t = n0 + n1
+    match, conf = torch.rand(t, generator=g), torch.rand(t, generator=g)
+    src = {"x32": torch.randn(t, 256, generator=g), "xm": torch.randn(t, 512, generator=g).to(torch.bfloat16),
+           "cs": torch.randn(t, 32, 2, generator=g)}
+    ind = torch.cat([torch.randperm(n0, generator=g), torch.randperm(n1, generator=g)]).to(torch.int32)
+    keep = match > 0.3
+    if with_conf:
+        keep = keep | (conf <= 0.6)
+    k0, k1 = torch.where(keep[:n0])[0], torch.where(keep[n0:])[0] + n0
+    sel = torch.cat([k0, k1])
+    d = {k: v.to(dev) for k, v in src.items()}
+    dst = {k: torch.zeros_like(v) for k, v in d.items()}
+    pos = torch.empty(t, dtype=torch.int32, device=dev)
+    counts = torch.zeros(4, dtype=torch.int32, device=dev)
+    ind_dst = torch.zeros(t, dtype=torch.int32, device=dev)
+    pr0 = torch.ones(1, n0, dtype=torch.int64, device=dev)
+    pr1 = torch.ones(1, n1, dtype=torch.int64, device=dev)
+    ops.lg_prune(match.to(dev), conf.to(dev) if with_conf else None, n0, n1, 0.3, 0.6, pos, counts, d, dst, ind.to(dev),
+                 ind_dst, pr0, pr1)
+    assert counts[:2].tolist() == [k0.numel(), k1.numel()]
+    n = sel.numel()
+    assert torch.equal(dst["x32"][:n].cpu(), src["x32"][sel])
+    assert torch.equal(dst["xm"][:n, :256].cpu(), src["xm"][sel, :256])
+    assert torch.equal(dst["cs"][:n].cpu(), src["cs"][sel])
+    assert torch.equal(ind_dst[:n].cpu(), ind[sel])
+    want0 = torch.ones(n0, dtype=torch.int64)
+    want0[ind[k0].long()] += 1
+    assert torch.equal(pr0[0].cpu(), want0)
+    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    ops.lg_count_below(conf.to(dev), t, 0.25, cnt)
+    assert cnt.item() == (conf < 0.25).sum().item()
+    # scatter back
+    m, nn = k0.numel(), k1.numel()
+    m0 = torch.randint(-1, nn, (1, m), generator=g)
+    m1 = torch.randint(-1, m, (1, nn), generator=g)
+    ms0, ms1 = torch.rand(1, m, generator=g), torch.rand(1, nn, generator=g)
+    o0 = torch.full((1, n0), -1, dtype=torch.int64, device=dev)
+    o1 = torch.full((1, n1), -1, dtype=torch.int64, device=dev)
+    s0, s1 = torch.zeros(1, n0, device=dev), torch.zeros(1, n1, device=dev)
+    ops.lg_scatter_matches(m0.to(dev), m1.to(dev), ms0.to(dev), ms1.to(dev), ind_dst, m, nn, o0, o1, s0, s1)
+    i0, i1 = ind[k0].long()[None], ind[k1].long()[None]
+    w0 = torch.full((1, n0), -1, dtype=torch.int64)
+    w0[:, i0[0]] = torch.where(m0 == -1, -1, i1.gather(1, m0.clamp(min=0)))
+    w1 = torch.full((1, n1), -1, dtype=torch.int64)
+    w1[:, i1[0]] = torch.where(m1 == -1, -1, i0.gather(1, m1.clamp(min=0)))
+    assert torch.equal(o0.cpu(), w0) and torch.equal(o1.cpu(), w1)
+    ws0 = torch.zeros(1, n0)
+    ws0[:, i0[0]] = ms0
+    assert torch.equal(s0.cpu(), ws0)
