@@ -231,6 +231,17 @@ int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius,
                        b200_stream_t stream) {
     return launch_nms_border(scores, B, H, W, nms_radius, remove_borders, out, static_cast<cudaStream_t>(stream));
 }
+int b200_sp_nms_border_list(const float* scores, int B, int H, int W, int nms_radius, int remove_borders, float* out,
+                            unsigned long long* candidates, int* candidate_state, int capacity, b200_stream_t stream) {
+    return launch_nms_list(scores, B, H, W, nms_radius, remove_borders, out, candidates, candidate_state, capacity,
+                           static_cast<cudaStream_t>(stream));
+}
+int b200_sp_select_topk_list(const float* nms_map, int B, int H, int W, float threshold, int k,
+                             const unsigned long long* candidates, int* candidate_state, int capacity,
+                             float* keypoints, float* scores, int* indices, int* counts, b200_stream_t stream) {
+    return launch_select_list(nms_map, B, H, W, threshold, k, candidates, candidate_state, capacity, keypoints, scores,
+                              indices, counts, static_cast<cudaStream_t>(stream));
+}
 int b200_sp_count_candidates(const float* nms_map, int B, int H, int W, float threshold, int* counts,
                              b200_stream_t stream) {
     return launch_count_candidates(nms_map, B, H, W, threshold, counts, static_cast<cudaStream_t>(stream));

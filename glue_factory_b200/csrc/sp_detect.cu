@@ -1,0 +1,415 @@
+// Bandwidth-bound SuperPoint detection, fast path: register-blocked separable NMS (radius 1..4) that
+// also emits a compact list of the surviving maxima, and a per-image top-k over that list.
+//
+// nms_list_kernel<R>: a CTA stages a 128 x 96 window of the score map (output tile + 5R halo: three
+// dependent max-pools of radius R plus two mask dilations).  Float pools are separable sliding-window
+// maxima held in registers (row pass: lanes along y, odd smem pitch; column pass: lanes along x);
+// the max / suppression masks live as bit rows (ballot), so the two dilations cost a few word ops.
+// Comparisons only => bit-exact with the reference's max_pool2d formulation
+// (reference: gluefactory/models/extractors/superpoint_open.py:34-49,147-152).
+//
+// select_list_kernel: per image, radix select of the k-th largest composite key
+// (score key << 32 | ~linear index: a total order, score descending then index ascending) over the
+// candidate list, then a bitonic sort of the k winners in shared memory
+// (reference: superpoint_open.py:52-56,155-179).  Images whose list cannot decide the result (list
+// overflow, or a negative threshold with fewer than k positive maxima so that zero-valued pixels
+// are selected) are flagged and handled by the full-map kernel in sp_select.cu.
+#include "common.cuh"
+#include "sp_kernels.cuh"
+
+namespace b200 {
+
+constexpr int kEW = 128, kEH = 96, kSeg = 16;
+constexpr int kNmsFastThreads = 256;
+constexpr int kMaskWords = 6;  // [guard | 4 words = 128 columns | guard]
+
+__device__ __forceinline__ uint32_t order_key32(float v) {
+    const uint32_t u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// o[i] = max(v[i .. i+2R]) for i < kSeg
+template <int R>
+__device__ __forceinline__ void window_max(const float (&v)[kSeg + 2 * R], float (&o)[kSeg]) {
+    constexpr int n = kSeg + 2 * R;
+    float m2[n - 1];
+#pragma unroll
+    for (int i = 0; i < n - 1; ++i) m2[i] = fmaxf(v[i], v[i + 1]);
+    if constexpr (R == 1) {
+#pragma unroll
+        for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(m2[i], v[i + 2]);
+    } else {
+        float m4[n - 3];
+#pragma unroll
+        for (int i = 0; i < n - 3; ++i) m4[i] = fmaxf(m2[i], m2[i + 2]);
+        if constexpr (R == 2) {
+#pragma unroll
+            for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(m4[i], v[i + 4]);
+        } else if constexpr (R == 3) {
+#pragma unroll
+            for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(m4[i], m4[i + 3]);
+        } else {
+            static_assert(R == 4, "radius 1..4");
+#pragma unroll
+            for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(fmaxf(m4[i], m4[i + 4]), v[i + 8]);
+        }
+    }
+}
+
+template <int R>
+struct NmsGeom {
+    static constexpr int kPitchS = kEW + 2 * R + 1;  // odd: lanes along y hit distinct banks
+    static constexpr int kPitchT = kEW + 1;
+    static constexpr int kTileW = kEW - 10 * R, kTileH = kEH - 10 * R;
+    static constexpr int kSFloats = kEH * kPitchS;
+    static constexpr int kTFloats = (kEH + 2 * R) * kPitchT;
+    static constexpr int kMaskRows = kEH + 2 * R;
+    static constexpr size_t kSmemBytes =
+        (size_t)(kSFloats + kTFloats) * 4 + (size_t)(kMaskRows + kEH) * kMaskWords * 4;
+};
+
+// row pass: tmp[y][x] = max_{|dx|<=R} src(y, x+dx), src = s or (supp ? 0 : s)
+template <int R, bool MASKED>
+__device__ __forceinline__ void row_pass(const float* __restrict__ s, float* __restrict__ tmp,
+                                         const uint32_t* __restrict__ supp) {
+    using G = NmsGeom<R>;
+    for (int item = threadIdx.x; item < kEH * (kEW / kSeg); item += kNmsFastThreads) {
+        const int y = item % kEH, x0 = (item / kEH) * kSeg;
+        float v[kSeg + 2 * R], o[kSeg];
+        const float* row = s + y * G::kPitchS + x0;  // column x0-R of the image window (array is shifted by R)
+#pragma unroll
+        for (int j = 0; j < kSeg + 2 * R; ++j) v[j] = row[j];
+        if constexpr (MASKED) {
+            // 32 suppression bits starting at column x0-R (guard words are zero)
+            const int p = x0 - R + 32;
+            const uint32_t* w = supp + y * kMaskWords + (p >> 5);
+            const uint32_t bits = __funnelshift_r(w[0], w[1], p & 31);
+#pragma unroll
+            for (int j = 0; j < kSeg + 2 * R; ++j)
+                if (((bits >> j) & 1u) && v[j] != -INFINITY) v[j] = 0.f;  // padding stays -inf
+        }
+        window_max<R>(v, o);
+        float* dst = tmp + (y + R) * G::kPitchT + x0;
+#pragma unroll
+        for (int i = 0; i < kSeg; ++i) dst[i] = o[i];
+    }
+}
+
+// column pass + comparison: bit(y, x) = s == max_{|dy|<=R} tmp(y+dy, x) [and not suppressed]
+template <int R, bool ROUND>
+__device__ __forceinline__ void col_pass(const float* __restrict__ s, const float* __restrict__ tmp,
+                                         uint32_t* __restrict__ mask, const uint32_t* __restrict__ supp) {
+    using G = NmsGeom<R>;
+    const int lane = threadIdx.x & 31;
+    for (int item = threadIdx.x; item < kEW * (kEH / kSeg); item += kNmsFastThreads) {
+        const int x = item & (kEW - 1), y0 = (item / kEW) * kSeg;
+        float v[kSeg + 2 * R], o[kSeg];
+#pragma unroll
+        for (int j = 0; j < kSeg + 2 * R; ++j) v[j] = tmp[(y0 + j) * G::kPitchT + x];
+        window_max<R>(v, o);
+        const int word = 1 + (x >> 5);  // warp-uniform
+#pragma unroll
+        for (int i = 0; i < kSeg; ++i) {
+            const float sv = s[(y0 + i) * G::kPitchS + R + x];
+            bool c = sv != -INFINITY && sv == o[i];  // out-of-image pixels never become maxima
+            if constexpr (ROUND) c = c && !((supp[(y0 + i) * kMaskWords + word] >> lane) & 1u);
+            const uint32_t b = __ballot_sync(0xffffffffu, c);
+            if (lane == 0) {
+                uint32_t* m = mask + (y0 + i + R) * kMaskWords + word;
+                *m = ROUND ? (*m | b) : b;
+            }
+        }
+    }
+}
+
+// supp = dilate(mask, R) (max_pool of the 0/1 mask > 0)
+template <int R>
+__device__ __forceinline__ void dilate(const uint32_t* __restrict__ mask, uint32_t* __restrict__ supp) {
+    for (int item = threadIdx.x; item < kEH * 4; item += kNmsFastThreads) {
+        const int y = item >> 2, w = 1 + (item & 3);
+        uint32_t l = 0, m = 0, r = 0;
+#pragma unroll
+        for (int dy = 0; dy <= 2 * R; ++dy) {
+            const uint32_t* row = mask + (y + dy) * kMaskWords + w;  // mask rows are shifted by R
+            l |= row[-1];
+            m |= row[0];
+            r |= row[1];
+        }
+        uint32_t d = m;
+#pragma unroll
+        for (int k = 1; k <= R; ++k) d |= (m << k) | (l >> (32 - k)) | (m >> k) | (r << (32 - k));
+        supp[y * kMaskWords + w] = d;
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(kNmsFastThreads, 2)
+nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, float* __restrict__ out,
+                unsigned long long* __restrict__ cand, int* __restrict__ cand_count, int cap) {
+    using G = NmsGeom<R>;
+    extern __shared__ uint8_t nms_fast_smem[];
+    float* s = reinterpret_cast<float*>(nms_fast_smem);
+    float* tmp = s + G::kSFloats;
+    uint32_t* mask = reinterpret_cast<uint32_t*>(tmp + G::kTFloats);  // [kMaskRows][6], rows shifted by R
+    uint32_t* supp = mask + G::kMaskRows * kMaskWords;                // [kEH][6]
+    const int b = blockIdx.z, tid = threadIdx.x;
+    const int ox = blockIdx.x * G::kTileW, oy = blockIdx.y * G::kTileH;  // output tile origin
+    const int x0 = ox - 5 * R, y0 = oy - 5 * R;                          // staged window origin
+    const float* src = scores + (long long)b * H * W;
+
+    for (int i = tid; i < kEH * G::kPitchS; i += kNmsFastThreads) {
+        const int yy = i / G::kPitchS, c = i - yy * G::kPitchS;
+        const int y = y0 + yy, x = x0 + c - R;
+        const bool in = c >= R && c < R + kEW && y >= 0 && y < H && x >= 0 && x < W;
+        s[i] = in ? __ldg(src + (long long)y * W + x) : -INFINITY;
+    }
+    for (int i = tid; i < R * G::kPitchT; i += kNmsFastThreads) {
+        tmp[i] = -INFINITY;
+        tmp[(kEH + R) * G::kPitchT + i] = -INFINITY;
+    }
+    for (int i = tid; i < (G::kMaskRows + kEH) * kMaskWords; i += kNmsFastThreads) mask[i] = 0u;
+    __syncthreads();
+
+    row_pass<R, false>(s, tmp, nullptr);
+    __syncthreads();
+    col_pass<R, false>(s, tmp, mask, nullptr);
+    __syncthreads();
+#pragma unroll 1
+    for (int round = 0; round < 2; ++round) {
+        dilate<R>(mask, supp);
+        __syncthreads();
+        row_pass<R, true>(s, tmp, supp);
+        __syncthreads();
+        col_pass<R, true>(s, tmp, mask, supp);
+        __syncthreads();
+    }
+
+    const int lane = tid & 31;
+    float* dst = out + (long long)b * H * W;
+    unsigned long long* list = cand ? cand + (long long)b * cap : nullptr;
+    // one warp per output row segment of 32 columns
+    constexpr int kSegs = (G::kTileW + 31) / 32;
+    for (int item = tid >> 5; item < G::kTileH * kSegs; item += kNmsFastThreads / 32) {
+        const int ty = item / kSegs, tx = (item - ty * kSegs) * 32 + lane;
+        const int y = oy + ty, x = ox + tx;
+        const bool valid = tx < G::kTileW && y < H && x < W;
+        const int ex = tx + 5 * R, ey = ty + 5 * R;
+        float v = 0.f;
+        bool keep = false;
+        if (valid) {
+            const bool mx = (mask[(ey + R) * kMaskWords + 1 + (ex >> 5)] >> (ex & 31)) & 1u;
+            const float sv = s[ey * G::kPitchS + R + ex];
+            v = mx ? sv : 0.f;
+            const bool border = pad > 0 && (y < pad || x < pad || y >= H - pad || x >= W - pad);
+            if (border) v = -1.f;
+            dst[(long long)y * W + x] = v;
+            keep = v > 0.f;
+        }
+        if (list != nullptr) {
+            const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
+            if (ballot != 0u) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(cand_count + b, __popc(ballot));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                const int slot = base + __popc(ballot & ((1u << lane) - 1u));
+                if (keep && slot < cap)
+                    list[slot] = (static_cast<unsigned long long>(order_key32(v)) << 32) |
+                                 ~static_cast<uint32_t>(y * W + x);
+            }
+        }
+    }
+}
+
+template <int R>
+static int launch_nms_fast(const float* scores, int B, int H, int W, int pad, float* out, unsigned long long* cand,
+                           int* cand_count, int cap, cudaStream_t stream) {
+    using G = NmsGeom<R>;
+    auto kern = nms_list_kernel<R>;
+    static bool configured = false;
+    if (!configured) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::kSmemBytes));
+        configured = true;
+    }
+    dim3 grid((W + G::kTileW - 1) / G::kTileW, (H + G::kTileH - 1) / G::kTileH, B);
+    kern<<<grid, kNmsFastThreads, G::kSmemBytes, stream>>>(scores, H, W, pad, out, cand, cand_count, cap);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+bool nms_fast_supported(int radius) { return radius >= 1 && radius <= 4; }
+
+int launch_nms_list(const float* scores, int B, int H, int W, int radius, int pad, float* out,
+                    unsigned long long* cand, int* cand_count, int cap, cudaStream_t stream) {
+    B200_REQUIRE(nms_fast_supported(radius), "nms (list variant): radius %d outside [1, 4]", radius);
+    B200_REQUIRE((long long)H * W < (1ll << 31), "nms: image too large");
+    if (B == 0) return 0;
+    if (cand != nullptr) {
+        B200_REQUIRE(cand_count != nullptr && cap > 0, "nms: candidate list needs a counter and a capacity");
+        B200_CHECK_CUDA(cudaMemsetAsync(cand_count, 0, sizeof(int) * 2 * B, stream));
+    }
+    switch (radius) {
+        case 1: return launch_nms_fast<1>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
+        case 2: return launch_nms_fast<2>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
+        case 3: return launch_nms_fast<3>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
+        default: return launch_nms_fast<4>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
+    }
+}
+
+// =============================================================================================
+// top-k over the candidate list
+// =============================================================================================
+constexpr int kListThreads = 1024;
+constexpr int kListMaxK = 16384;
+
+__device__ __forceinline__ int block_sum_1024(int v, int* scratch /*[33]*/) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if (lane == 0) scratch[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        int t = scratch[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (lane == 0) scratch[32] = t;
+    }
+    __syncthreads();
+    return scratch[32];
+}
+
+__global__ void __launch_bounds__(kListThreads)
+select_list_kernel(const float* __restrict__ map, int H, int W, float thr, int k,
+                   const unsigned long long* __restrict__ cand, int* __restrict__ cand_count, int cap,
+                   float* __restrict__ kpts, float* __restrict__ kscores, int* __restrict__ kidx,
+                   int* __restrict__ counts) {
+    extern __shared__ unsigned long long keys[];  // [pow2 >= k]
+    __shared__ int hist[256];
+    __shared__ int scratch[33];
+    __shared__ int s_fill, s_bin, s_remaining, s_done;
+    const int b = blockIdx.x, tid = threadIdx.x, B = gridDim.x;
+    int* flag = cand_count + B + b;
+    const int n_raw = cand_count[b];
+    if (n_raw > cap) {  // list overflow: the full-map kernel decides
+        if (tid == 0) *flag = 1;
+        return;
+    }
+    const unsigned long long* list = cand + (long long)b * cap;
+    const uint32_t thr_key = order_key32(thr);
+    int c = 0;
+    for (int i = tid; i < n_raw; i += kListThreads) c += static_cast<uint32_t>(list[i] >> 32) > thr_key;
+    const int n = block_sum_1024(c, scratch);
+    if (thr < 0.f && n < k) {  // zero-valued pixels would be selected: not in the list
+        if (tid == 0) *flag = 1;
+        return;
+    }
+    const int count = n < k ? n : k;
+    if (tid == 0) { *flag = 0; counts[b] = count; s_fill = 0; }
+    int P = 1;
+    while (P < count) P <<= 1;
+    for (int i = tid; i < P; i += kListThreads) keys[i] = 0ull;
+    __syncthreads();
+    const bool by_index = n <= k;
+    if (by_index) {
+        for (int i = tid; i < n_raw; i += kListThreads) {
+            const unsigned long long e = list[i];
+            if (static_cast<uint32_t>(e >> 32) > thr_key) {
+                const int slot = atomicAdd(&s_fill, 1);
+                keys[slot] = (e << 32) | (e >> 32);  // (~index, score key): descending sort = row-major order
+            }
+        }
+    } else {
+        // radix select of the k-th largest 64-bit composite key; keys are unique, so no tie handling
+        unsigned long long prefix = 0ull, pmask = 0ull;
+        int remaining = k;
+        for (int pass = 0; pass < 8; ++pass) {
+            const int shift = 56 - 8 * pass;
+            for (int i = tid; i < 256; i += kListThreads) hist[i] = 0;
+            __syncthreads();
+            for (int i = tid; i < n_raw; i += kListThreads) {
+                const unsigned long long e = list[i];
+                if (static_cast<uint32_t>(e >> 32) > thr_key && (e & pmask) == prefix)
+                    atomicAdd(&hist[(int)((e >> shift) & 255ull)], 1);
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int cum = 0, bin = 255;
+                for (; bin > 0; --bin) {
+                    if (cum + hist[bin] >= remaining) break;
+                    cum += hist[bin];
+                }
+                s_bin = bin;
+                s_remaining = remaining - cum;
+                s_done = hist[bin] == remaining - cum;  // the whole bin is taken: threshold = prefix
+            }
+            __syncthreads();
+            prefix |= static_cast<unsigned long long>(s_bin) << shift;
+            pmask |= 0xFFull << shift;
+            remaining = s_remaining;
+            const int done = s_done;
+            __syncthreads();
+            if (done) break;
+        }
+        for (int i = tid; i < n_raw; i += kListThreads) {
+            const unsigned long long e = list[i];
+            if (static_cast<uint32_t>(e >> 32) > thr_key && e >= prefix) {
+                const int slot = atomicAdd(&s_fill, 1);
+                if (slot < P) keys[slot] = e;
+            }
+        }
+    }
+    __syncthreads();
+    for (int size = 2; size <= P; size <<= 1) {
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = tid; t < (P >> 1); t += kListThreads) {
+                const int lo = ((t / stride) * stride << 1) + (t % stride), hi = lo + stride;
+                const bool desc = (lo & size) == 0;
+                const unsigned long long a = keys[lo], c2 = keys[hi];
+                if ((a < c2) == desc) { keys[lo] = c2; keys[hi] = a; }
+            }
+            __syncthreads();
+        }
+    }
+    const float* m = map + (long long)b * H * W;
+    for (int j = tid; j < k; j += kListThreads) {
+        const long long o = (long long)b * k + j;
+        if (j < count) {
+            const unsigned long long key = keys[j];
+            const uint32_t idx = by_index ? ~static_cast<uint32_t>(key >> 32) : ~static_cast<uint32_t>(key);
+            const int y = idx / W, x = idx - y * W;
+            kpts[o * 2] = x + 0.5f;
+            kpts[o * 2 + 1] = y + 0.5f;
+            kscores[o] = m[idx];
+            kidx[o] = static_cast<int>(idx);
+        } else {
+            kpts[o * 2] = 0.f;
+            kpts[o * 2 + 1] = 0.f;
+            kscores[o] = 0.f;
+            kidx[o] = -1;
+        }
+    }
+}
+
+int launch_select_list(const float* nms_map, int B, int H, int W, float threshold, int k,
+                       const unsigned long long* cand, int* cand_count, int cap, float* kpts, float* kscores,
+                       int* kidx, int* counts, cudaStream_t stream) {
+    B200_REQUIRE(k >= 1 && k <= kListMaxK, "select_topk: k=%d outside [1, %d]", k, kListMaxK);
+    B200_REQUIRE(cand && cand_count && cap > 0, "select_topk (list variant): null candidate list");
+    if (B == 0) return 0;
+    int P = 1;
+    while (P < k) P <<= 1;
+    const size_t smem = (size_t)P * sizeof(unsigned long long);
+    static size_t configured = 0;
+    if (smem > configured) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(select_list_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    select_list_kernel<<<B, kListThreads, smem, stream>>>(nms_map, H, W, threshold, k, cand, cand_count, cap, kpts,
+                                                          kscores, kidx, counts);
+    B200_CHECK_CUDA(cudaGetLastError());
+    // flagged images (cand_count[B + b] != 0) are redone from the full map
+    return launch_select_topk_flagged(nms_map, B, H, W, threshold, k, kpts, kscores, kidx, counts, cand_count + B,
+                                      stream);
+}
+
+}  // namespace b200

@@ -8,19 +8,18 @@ namespace b200 {
 
 // =============================================================================================
 // conv1a: gray (or RGB -> gray) image, 3x3 conv 1 -> 64, bias, ReLU, BN affine, NHWC bf16 output.
-// K = 9 is useless on tensor cores, so this runs on the CUDA cores; one thread per pixel.
+// K = 9 is useless on tensor cores, so this runs on the CUDA cores.  A thread owns 8 output channels
+// (their 72 weights live in registers) and walks down a column of the tile, so a warp store covers
+// 4 pixels x 128 B of contiguous NHWC output and each new pixel costs 3 shared-memory reads.
 // =============================================================================================
-constexpr int kC1TileW = 32, kC1TileH = 8;
+constexpr int kC1TileW = 32, kC1TileH = 32;
 
-__global__ void __launch_bounds__(256) conv1a_kernel(const float* __restrict__ img, int C, int H, int W,
-                                                     const float* __restrict__ w, const float* __restrict__ bias,
-                                                     const float* __restrict__ scale, const float* __restrict__ shift,
-                                                     __nv_bfloat16* __restrict__ out) {
+__global__ void __launch_bounds__(256, 2) conv1a_kernel(const float* __restrict__ img, int C, int H, int W,
+                                                        const float* __restrict__ w, const float* __restrict__ bias,
+                                                        const float* __restrict__ scale, const float* __restrict__ shift,
+                                                        __nv_bfloat16* __restrict__ out) {
     __shared__ float tile[kC1TileH + 2][kC1TileW + 2];
-    __shared__ float sw[64 * 9], sb[64], ss[64], sh[64];
-    const int tid = threadIdx.y * kC1TileW + threadIdx.x;
-    for (int i = tid; i < 64 * 9; i += 256) sw[i] = w[i];
-    if (tid < 64) { sb[tid] = bias[tid]; ss[tid] = scale[tid]; sh[tid] = shift[tid]; }
+    const int tid = threadIdx.x;
     const int b = blockIdx.z, x0 = blockIdx.x * kC1TileW, y0 = blockIdx.y * kC1TileH;
     const float* base = img + (long long)b * C * H * W;
     for (int i = tid; i < (kC1TileH + 2) * (kC1TileW + 2); i += 256) {
@@ -31,47 +30,67 @@ __global__ void __launch_bounds__(256) conv1a_kernel(const float* __restrict__ i
             const long long o = (long long)y * W + x;
             if (C == 3) {
                 // same association order as (image * [0.299, 0.587, 0.114]).sum(1)
-                v = base[o] * 0.299f;
-                v += base[o + (long long)H * W] * 0.587f;
-                v += base[o + 2ll * H * W] * 0.114f;
+                v = __ldg(base + o) * 0.299f;
+                v += __ldg(base + o + (long long)H * W) * 0.587f;
+                v += __ldg(base + o + 2ll * H * W) * 0.114f;
             } else {
-                v = base[o];
+                v = __ldg(base + o);
             }
         }
         tile[ty][tx] = v;
     }
+    const int cg = tid & 7, px = tid >> 3;  // channel group (8 channels), pixel column inside the tile
+    float wr[8][9], bi[8], sc[8], sh[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = cg * 8 + j;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) wr[j][t] = __ldg(w + c * 9 + t);
+        bi[j] = __ldg(bias + c);
+        sc[j] = __ldg(scale + c);
+        sh[j] = __ldg(shift + c);
+    }
     __syncthreads();
-    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
-    if (x >= W || y >= H) return;
+    const int x = x0 + px;
+    if (x >= W) return;
     float in[9];
 #pragma unroll
-    for (int dy = 0; dy < 3; ++dy)
+    for (int dx = 0; dx < 3; ++dx) {
+        in[3 + dx] = tile[0][px + dx];
+        in[6 + dx] = tile[1][px + dx];
+    }
+    const int rows = min(kC1TileH, H - y0);
+    __nv_bfloat16* o = out + ((long long)(b * H + y0) * W + x) * 64 + cg * 8;
+#pragma unroll 2
+    for (int ty = 0; ty < rows; ++ty) {
 #pragma unroll
-        for (int dx = 0; dx < 3; ++dx) in[dy * 3 + dx] = tile[threadIdx.y + dy][threadIdx.x + dx];
-    __nv_bfloat16* o = out + ((long long)(b * H + y) * W + x) * 64;
-#pragma unroll 1
-    for (int c0 = 0; c0 < 64; c0 += 8) {
+        for (int dx = 0; dx < 3; ++dx) {
+            in[dx] = in[3 + dx];
+            in[3 + dx] = in[6 + dx];
+            in[6 + dx] = tile[ty + 2][px + dx];
+        }
         float v[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float* wc = sw + (c0 + j) * 9;
-            float a = sb[c0 + j];
+            float a = bi[j];
 #pragma unroll
-            for (int t = 0; t < 9; ++t) a = fmaf(in[t], wc[t], a);
+            for (int t = 0; t < 9; ++t) a = fmaf(in[t], wr[j][t], a);
             a = fmaxf(a, 0.f);
-            v[j] = a * ss[c0 + j] + sh[c0 + j];
+            v[j] = a * sc[j] + sh[j];
         }
-        *reinterpret_cast<uint4*>(o + c0) =
+        *reinterpret_cast<uint4*>(o) =
             make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+        o += (long long)W * 64;
     }
 }
 
 int launch_conv1a(const float* img, int B, int C, int H, int W, const float* w, const float* bias,
                   const float* scale, const float* shift, void* out, cudaStream_t stream) {
     B200_REQUIRE(C == 1 || C == 3, "conv1a: image must have 1 or 3 channels, got %d", C);
-    dim3 grid((W + kC1TileW - 1) / kC1TileW, (H + kC1TileH - 1) / kC1TileH, B), block(kC1TileW, kC1TileH);
-    conv1a_kernel<<<grid, block, 0, stream>>>(img, C, H, W, w, bias, scale, shift,
-                                              reinterpret_cast<__nv_bfloat16*>(out));
+    if (B == 0) return 0;
+    dim3 grid((W + kC1TileW - 1) / kC1TileW, (H + kC1TileH - 1) / kC1TileH, B);
+    conv1a_kernel<<<grid, 256, 0, stream>>>(img, C, H, W, w, bias, scale, shift,
+                                            reinterpret_cast<__nv_bfloat16*>(out));
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

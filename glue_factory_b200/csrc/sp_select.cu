@@ -44,8 +44,10 @@ __global__ void __launch_bounds__(kSelThreads) count_candidates_kernel(const flo
 __global__ void __launch_bounds__(kSelThreads) select_topk_kernel(const float* __restrict__ map, int H, int W,
                                                                   float thr, int k, float* __restrict__ kpts,
                                                                   float* __restrict__ kscores, int* __restrict__ kidx,
-                                                                  int* __restrict__ counts) {
+                                                                  int* __restrict__ counts,
+                                                                  const int* __restrict__ only_flagged) {
     extern __shared__ unsigned long long keys[];  // [pow2 >= k]
+    if (only_flagged != nullptr && only_flagged[blockIdx.x] == 0) return;  // decided by the list kernel
     __shared__ int hist[257];
     __shared__ int scratch[33];
     __shared__ int thread_cnt[kSelThreads];
@@ -192,8 +194,8 @@ int launch_count_candidates(const float* nms_map, int B, int H, int W, float thr
     return 0;
 }
 
-int launch_select_topk(const float* nms_map, int B, int H, int W, float threshold, int k, float* kpts,
-                       float* kscores, int* kidx, int* counts, cudaStream_t stream) {
+int launch_select_topk_flagged(const float* nms_map, int B, int H, int W, float threshold, int k, float* kpts,
+                               float* kscores, int* kidx, int* counts, const int* only_flagged, cudaStream_t stream) {
     B200_REQUIRE(k >= 1 && k <= kSelMaxK, "select_topk: k=%d outside [1, %d]", k, kSelMaxK);
     if (B == 0) return 0;
     int P = 1;
@@ -204,9 +206,15 @@ int launch_select_topk(const float* nms_map, int B, int H, int W, float threshol
         B200_CHECK_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    select_topk_kernel<<<B, kSelThreads, smem, stream>>>(nms_map, H, W, threshold, k, kpts, kscores, kidx, counts);
+    select_topk_kernel<<<B, kSelThreads, smem, stream>>>(nms_map, H, W, threshold, k, kpts, kscores, kidx, counts,
+                                                         only_flagged);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+int launch_select_topk(const float* nms_map, int B, int H, int W, float threshold, int k, float* kpts,
+                       float* kscores, int* kidx, int* counts, cudaStream_t stream) {
+    return launch_select_topk_flagged(nms_map, B, H, W, threshold, k, kpts, kscores, kidx, counts, nullptr, stream);
 }
 
 // =============================================================================================

@@ -162,8 +162,12 @@ class SuperPoint(BaseModel):
     def detect(self, heat):
         """heat map -> (keypoints (B,K,2) incl. +0.5, scores (B,K), counts (B,) int32 on device)."""
         c = self.conf
-        nms = ops.sp_nms_border(heat, c.nms_radius, c.remove_borders)
         k = c.max_num_keypoints
+        if k is not None and 1 <= c.nms_radius <= 4:
+            _, kpts, scores, _, counts = ops.sp_detect_fast(heat, c.nms_radius, c.remove_borders,
+                                                            c.detection_threshold, k)
+            return kpts, scores, counts
+        nms = ops.sp_nms_border(heat, c.nms_radius, c.remove_borders)
         if k is None:
             k = int(ops.sp_count_candidates(nms, c.detection_threshold).max().item())  # host sync, as in the reference
             k = max(k, 1)

@@ -146,6 +146,32 @@ def sp_nms_border(scores, radius, pad):
     return out
 
 
+CANDIDATE_CAPACITY = 1 << 16  # surviving maxima kept per image by the fast detection path
+
+
+def sp_detect_fast(scores, radius, pad, threshold, k):
+    """NMS + border removal + top-k through the candidate list (nms_radius 1..4).
+    Returns (nms_map, keypoints, scores, indices, counts)."""
+    _require_cuda(scores)
+    b, h, w = scores.shape
+    dev = scores.device
+    nms = torch.empty_like(scores)
+    cand = torch.empty(b, CANDIDATE_CAPACITY, dtype=torch.int64, device=dev)
+    state = torch.empty(2 * b, dtype=torch.int32, device=dev)
+    with _timed("sp_nms_border", 2, 8.0 * b * h * w):
+        _lib.check(_lib.lib().b200_sp_nms_border_list(_ptr(scores), b, h, w, int(radius), int(pad or 0), _ptr(nms),
+                                                      _ptr(cand), _ptr(state), CANDIDATE_CAPACITY, _stream()))
+    kpts = torch.empty(b, k, 2, dtype=torch.float32, device=dev)
+    ksc = torch.empty(b, k, dtype=torch.float32, device=dev)
+    idx = torch.empty(b, k, dtype=torch.int32, device=dev)
+    counts = torch.empty(b, dtype=torch.int32, device=dev)
+    with _timed("sp_select_topk", 2, 4.0 * b * h * w):
+        _lib.check(_lib.lib().b200_sp_select_topk_list(_ptr(nms), b, h, w, float(threshold), int(k), _ptr(cand),
+                                                       _ptr(state), CANDIDATE_CAPACITY, _ptr(kpts), _ptr(ksc),
+                                                       _ptr(idx), _ptr(counts), _stream()))
+    return nms, kpts, ksc, idx, counts
+
+
 def sp_count_candidates(nms_map, threshold):
     b, h, w = nms_map.shape
     counts = torch.empty(b, dtype=torch.int32, device=nms_map.device)

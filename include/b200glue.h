@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 1
+#define B200_ABI_VERSION 2
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -107,6 +107,17 @@ int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* 
 /* batched_nms (:34-49) + border removal (:147-152); out has the shape of scores */
 int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
                        float* out, b200_stream_t stream);
+/* Fast path of the two entries above and below for nms_radius 1..4: the NMS pass also appends every
+ * surviving positive maximum to a per-image list candidates[B][capacity] (64-bit records: monotone score
+ * key << 32 | ~linear index), counted in candidate_state[0..B) (candidate_state has 2*B ints and is
+ * zeroed by the call); b200_sp_select_topk_list then selects from the list, and re-does from the full map
+ * only the images whose list cannot decide the result (overflow, or zero-score pixels among the top k). */
+int b200_sp_nms_border_list(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
+                            float* out, unsigned long long* candidates, int* candidate_state, int capacity,
+                            b200_stream_t stream);
+int b200_sp_select_topk_list(const float* nms_map, int B, int H, int W, float threshold, int k,
+                             const unsigned long long* candidates, int* candidate_state, int capacity,
+                             float* keypoints, float* scores, int* indices, int* counts, b200_stream_t stream);
 /* number of pixels above the detection threshold per image (:155-160) */
 int b200_sp_count_candidates(const float* nms_map, int B, int H, int W, float threshold, int* counts,
                              b200_stream_t stream);

@@ -79,6 +79,57 @@ def test_select_topk_large_map_with_massive_ties(dev):
         assert torch.equal(scores[b].cpu(), sc)
 
 
+def _check_detect_fast(dev, s, r, pad, thr, k):
+    from glue_factory_b200 import ops
+
+    want_map = osp.remove_borders(osp.nms(s, r), pad) if pad else osp.nms(s, r)
+    nms, kpts, scores, idx, counts = ops.sp_detect_fast(s.to(dev), r, pad, thr, k)
+    torch.cuda.synchronize()
+    assert torch.equal(nms.cpu(), want_map), f"{(nms.cpu() != want_map).sum().item()} NMS pixels differ"
+    for b in range(s.shape[0]):
+        xy, sc, li = osp.select_keypoints(want_map[b], thr, k)
+        n = li.numel()
+        assert counts[b].item() == n
+        assert torch.equal(idx[b, :n].cpu().long(), li)
+        assert torch.equal(scores[b, :n].cpu(), sc)
+        assert torch.equal(kpts[b, :n].cpu(), xy + 0.5)
+
+
+@pytest.mark.parametrize("r", [1, 2, 3, 4])
+@pytest.mark.parametrize("shape", [(1, 64, 64), (2, 97, 131), (1, 200, 70), (2, 300, 260)])
+@pytest.mark.parametrize("plateaus", [False, True])
+def test_detect_fast_bit_exact(dev, r, shape, plateaus):
+    """register-blocked NMS + candidate-list top-k (fast path) against the oracle, all tile-edge cases"""
+    s = _scores(r * 13 + shape[2], *shape, plateaus=plateaus)
+    _check_detect_fast(dev, s, r, 4, 0.005, 100)
+
+
+@pytest.mark.parametrize("thr,k", [(0.0, 300), (-1.0, 128), (-1.0, 4000), (0.5, 4096), (2.0, 16), (0.9, 7)])
+@pytest.mark.parametrize("plateaus", [False, True])
+def test_detect_fast_thresholds(dev, thr, k, plateaus):
+    """few / no candidates, all candidates kept (row-major order), zero-score pixels among the top k
+    (negative threshold: the full-map kernel takes over for that image)"""
+    s = _scores(17, 3, 72, 88, plateaus=plateaus)
+    _check_detect_fast(dev, s, 2, 4, thr, k)
+
+
+def test_detect_fast_no_border(dev):
+    _check_detect_fast(dev, _scores(5, 1, 80, 96), 3, 0, 0.1, 64)
+
+
+def test_detect_fast_list_overflow(dev):
+    """radius 1 on white noise leaves > 65536 maxima per megapixel image: the list overflows and the
+    full-map kernel must produce the result"""
+    s = _scores(23, 1, 1024, 1024)
+    _check_detect_fast(dev, s, 1, 4, 0.0, 2048)
+
+
+def test_detect_fast_config2_shape(dev):
+    s = _scores(29, 2, 1024, 1024) ** 4
+    _check_detect_fast(dev, s, 3, 4, -1.0, 2048)
+    _check_detect_fast(dev, s, 4, 4, 0.005, 2048)
+
+
 def test_sample_descriptors(dev):
     from glue_factory_b200 import ops
 
