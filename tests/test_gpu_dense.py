@@ -174,7 +174,8 @@ def _attn_ref(q, k, v, scale):
     return torch.softmax(s, -1) @ v.float()
 
 
-@pytest.mark.parametrize("lens", [[(128, 128)], [(200, 333), (77, 130)], [(2048, 2048)]])
+@pytest.mark.parametrize("lens", [[(128, 128)], [(200, 333), (77, 130)], [(2048, 2048)], [(129, 64), (256, 257), (300, 1)],
+                                  [(513, 700), (1, 5), (640, 384)]])
 def test_attention(dev, lens):
     from glue_factory_b200 import ops
 
