@@ -1,6 +1,7 @@
 // C-ABI entry points (include/b200glue.h): argument checks, TMA tensor-map construction, launches.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -25,6 +26,8 @@ void set_last_error(const char* fmt, ...) {
 
 int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const CUtensorMap& tb,
                 const GemmParams& p, int num_sms, cudaStream_t stream);
+int launch_conv_patch(int cout, const CUtensorMap& ta, const CUtensorMap& tw, const GemmParams& p, int num_sms,
+                      cudaStream_t stream);
 int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                      int num_seqs, int max_q_len, int heads, cudaStream_t stream);
 
@@ -112,6 +115,11 @@ static int make_map_2d(CUtensorMap* out, const void* ptr, long long rows, long l
     return make_map(out, ptr, 2, dims, strides, box);
 }
 
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
 static int sm_count() {
     static int n = 0;
     if (n == 0) {
@@ -183,6 +191,18 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
                      "gemm: softmax/depth-to-space epilogue needs N == 65, block_n == 80 and the cell grid");
 
     CUtensorMap ta, tb;
+    if (d->conv && d->Cin == 64 && d->N == 64 && epi == B200_EPI_CONV_RELU_BN && d->K == 576 &&
+        d->ldb == 576 && env_int("B200_CONV_PATCH", 1) != 0) {
+        // C_in = 64 layers: halo patch loaded once per tile, nine taps addressed inside it (conv_patch.cu)
+        p.H = d->H; p.W = d->W; p.Cin = 64;
+        p.tiles_x = (d->W + 7) / 8; p.tiles_y = (d->H + 15) / 16;
+        const uint64_t dims[4] = {64, (uint64_t)d->W, (uint64_t)d->H, (uint64_t)d->batch};
+        const uint64_t strides[3] = {128, (uint64_t)d->W * 128, (uint64_t)d->H * d->W * 128};
+        const uint32_t box[4] = {64, 16, 18, 1};
+        if (make_map(&ta, d->a, 4, dims, strides, box) != 0) return -1;
+        if (make_map_2d(&tb, d->b, d->N, 576, 576, (uint32_t)d->N) != 0) return -1;
+        return launch_conv_patch(d->N, ta, tb, p, num_sms, stream);
+    }
     const uint32_t b_box = d->block_n > 256 ? 256u : (uint32_t)d->block_n;
     if (make_map_2d(&tb, d->b, d->b_rows, d->K, d->ldb, b_box) != 0) return -1;
     int a_mode = 0;
