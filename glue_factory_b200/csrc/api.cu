@@ -181,6 +181,8 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
         B200_REQUIRE(d->N == 512 && d->block_n == 512 && d->bias && d->ln_gamma && d->ln_beta,
                      "gemm: LayerNorm epilogue needs N == block_n == 512 and bias/gamma/beta");
     if (epi == B200_EPI_F32) B200_REQUIRE(d->out32 != nullptr, "gemm: fp32 epilogue needs out32");
+    B200_REQUIRE(d->N <= 768 || (d->bias == nullptr && d->scale == nullptr && d->shift == nullptr),
+                 "gemm: per-column epilogue operands are staged for N <= 768 (N=%d)", d->N);
     if (epi == B200_EPI_CONV_RELU_BN || epi == B200_EPI_CONV_BN_L2 || epi == B200_EPI_CONV_BN_SOFTMAX_D2S)
         B200_REQUIRE(d->bias && d->scale && d->shift, "gemm: conv epilogues need bias, scale and shift");
     if (epi == B200_EPI_CONV_BN_L2)

@@ -4,7 +4,9 @@
 //
 // * warp 0: TMA producer (A and B tiles, 128-byte swizzle, ring of kStages smem slots)
 // * warp 1: TMEM allocation + single-thread tcgen05.mma issue, tcgen05.commit to mbarriers
-// * warps 2-5: epilogue, one accumulator row (TMEM lane) per thread, fused element-wise work
+// * warps 2-9: epilogue, two warps per TMEM lane quarter taking alternate 32-column chunks; per-column
+//   operands come from shared memory; row-major outputs are staged per warp in shared memory so global
+//   loads / stores (residual, fp32 / bf16 outputs) are coalesced 128-byte row segments
 // The accumulator is double buffered in TMEM (except BLOCK_N = 512) so the epilogue of tile i
 // overlaps the main loop of tile i+1.  With A_MODE = 1 the A operand is gathered by 4-D TMA boxes
 // from an NHWC activation tensor (implicit-GEMM 3x3 convolution; out-of-bounds box elements are
@@ -21,22 +23,27 @@ namespace b200 {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int kTileH = 8, kTileW = 16;  // conv M-tile: 8 x 16 pixels
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;            // two warps per TMEM lane quarter, interleaved 32-column chunks
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
+constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged in smem (bias | scale/gamma | shift/beta)
+constexpr int kStageBytesPerWarp = 4096;  // 32 rows x 128 B staging per epilogue warp
+constexpr int kEpiSmemBytes = kParamFloats * 4 + kEpiWarps * kStageBytesPerWarp + 128 * 2 * 8;
 
 template <int BLOCK_N>
 struct GemmCfg {
     static constexpr int kABytes = kBlockM * kBlockK * 2;
     static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (200 * 1024 / kStageBytes) > 8 ? 8 : (200 * 1024 / kStageBytes);
+    static constexpr int kStages = (176 * 1024 / kStageBytes) > 8 ? 8 : (176 * 1024 / kStageBytes);
     static constexpr int kAccStages = BLOCK_N <= 256 ? 2 : 1;
     static constexpr int kAccStride = BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : (BLOCK_N <= 256 ? 256 : 512));
     static constexpr int kTmemCols = kAccStride * kAccStages < 32 ? 32 : kAccStride * kAccStages;
     static constexpr int kUmmaN = BLOCK_N > 256 ? 256 : BLOCK_N;
     static constexpr int kNumUmmaN = BLOCK_N / kUmmaN;
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiSmemBytes;
     static_assert(kStageBytes % 1024 == 0, "stage must keep 1024-byte alignment for SWIZZLE_128B");
     static_assert(kTmemCols <= 512, "TMEM budget");
+    static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
 __device__ __forceinline__ float gelu_erf(float x) {
@@ -47,108 +54,164 @@ __device__ __forceinline__ void store16B(void* p, uint32_t a, uint32_t b, uint32
     *reinterpret_cast<uint4*>(p) = make_uint4(a, b, c, d);
 }
 
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
+
+// epilogue-side view of shared memory
+struct EpiSmem {
+    const float* bias;    // [768]
+    const float* par1;    // [768] scale / LayerNorm gamma
+    const float* par2;    // [768] shift / LayerNorm beta
+    uint8_t* stage;       // this warp's 4 KB staging tile
+    float2* exch;         // [2][128] per-row partial statistics exchanged between the two column halves
+};
+
 // ---------------------------------------------------------------------------------------------
-// epilogue bodies: `acc_taddr` addresses column 0 of this tile's accumulator for this warp's lanes
+// epilogue bodies.  `acc_taddr` addresses column 0 of this tile's accumulator for this warp's TMEM
+// lanes.  Two warps share a lane quarter and take alternate 32-column chunks (`half`).
+// Row-major outputs go through a per-warp staging tile so that global loads / stores are coalesced:
+// phase A: thread <-> accumulator row (per-column math), phase B: 8 lanes <-> one 128-byte row segment.
 // ---------------------------------------------------------------------------------------------
 template <int BLOCK_N, int EPI>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_taddr, int batch,
-                                              long long row_in_batch, bool row_valid, int n0, int lane,
-                                              int img, int py, int px) {
+__device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem& es, uint32_t acc_taddr, int batch,
+                                              long long tile_row0, int half, int n0, int lane) {
     uint32_t r[32];
-    if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_QKV_ROTARY || EPI == EPI_RESID || EPI == EPI_F32) {
-        const long long grow = (long long)batch * p.M + row_in_batch;  // global output row
+    const bool has_bias = p.bias != nullptr;
+    const long long row_base = (long long)batch * p.M;
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 32; ++c) {
-            const int col0 = n0 + c * 32;
-            if (col0 >= p.N) break;  // warp-uniform
-            tmem_ld32(acc_taddr + c * 32, r);
-            tmem_ld_wait();
-            float v[32];
+    for (int c = half; c < BLOCK_N / 32; c += 2) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        tmem_ld32(acc_taddr + c * 32, r);
+        tmem_ld_wait();
+        uint8_t* myrow = es.stage + lane * 128;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                v[i] = __uint_as_float(r[i]);
-                if (EPI == EPI_F32) v[i] *= p.alpha;
-                if (p.bias != nullptr && col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
+        for (int q = 0; q < 8; ++q) {
+            float4 v = make_float4(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1]),
+                                   __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
+            if (EPI == EPI_F32) { v.x *= p.alpha; v.y *= p.alpha; v.z *= p.alpha; v.w *= p.alpha; }
+            if (has_bias) {
+                const float4 b = *reinterpret_cast<const float4*>(es.bias + col0 + q * 4);
+                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
             }
+            *reinterpret_cast<float4*>(myrow + ((q ^ (lane & 7)) << 4)) = v;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3), cj = lane & 7;
+            float4 v = *reinterpret_cast<const float4*>(es.stage + rr * 128 + ((cj ^ (rr & 7)) << 4));
+            const long long row_in_batch = tile_row0 + rr;
+            if (row_in_batch >= p.M) continue;
+            const long long grow = row_base + row_in_batch;
+            const int col = col0 + cj * 4;
             if constexpr (EPI == EPI_QKV_ROTARY) {
-                if (col0 < p.rot_cols && row_valid) {
-                    const float2* cs = p.cs + grow * 32 + ((col0 & 63) >> 1);
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float2 t = __ldg(cs + i);
-                        const float x0 = v[2 * i], x1 = v[2 * i + 1];
-                        v[2 * i] = x0 * t.x - x1 * t.y;
-                        v[2 * i + 1] = x1 * t.x + x0 * t.y;
-                    }
+                if (col0 < p.rot_cols) {
+                    // (cos, sin) of frequencies (col & 63) / 2 and + 1
+                    const float4 t = __ldg(reinterpret_cast<const float4*>(p.cs + grow * 32 + ((col & 63) >> 1)));
+                    const float x0 = v.x, x1 = v.y, x2 = v.z, x3 = v.w;
+                    v.x = x0 * t.x - x1 * t.y;
+                    v.y = x1 * t.x + x0 * t.y;
+                    v.z = x2 * t.z - x3 * t.w;
+                    v.w = x3 * t.z + x2 * t.w;
                 }
             }
-            if (!row_valid) continue;
             if constexpr (EPI == EPI_RESID) {
-                float* o32 = p.out32 + grow * p.ld32 + col0;
-                const float* rs = p.resid + grow * p.ld32 + col0;
-#pragma unroll
-                for (int i = 0; i < 32; i += 4) {
-                    const float4 t = *reinterpret_cast<const float4*>(rs + i);
-                    v[i] += t.x; v[i + 1] += t.y; v[i + 2] += t.z; v[i + 3] += t.w;
-                    *reinterpret_cast<float4*>(o32 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-                }
+                const float4 t = *reinterpret_cast<const float4*>(p.resid + grow * p.ld32 + col);
+                v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+                *reinterpret_cast<float4*>(p.out32 + grow * p.ld32 + col) = v;
             }
             if constexpr (EPI == EPI_F32) {
-                float* o32 = p.out32 + (long long)batch * p.out32_batch_stride + row_in_batch * p.ld32 + col0;
-                if ((p.ld32 & 3) == 0 && col0 + 32 <= p.N) {
-#pragma unroll
-                    for (int i = 0; i < 32; i += 4)
-                        *reinterpret_cast<float4*>(o32 + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+                float* o32 = p.out32 + (long long)batch * p.out32_batch_stride + row_in_batch * p.ld32 + col;
+                if ((p.ld32 & 3) == 0 && col + 4 <= p.N) {
+                    *reinterpret_cast<float4*>(o32) = v;
                 } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (col0 + i < p.N) o32[i] = v[i];
+                    if (col < p.N) o32[0] = v.x;
+                    if (col + 1 < p.N) o32[1] = v.y;
+                    if (col + 2 < p.N) o32[2] = v.z;
+                    if (col + 3 < p.N) o32[3] = v.w;
                 }
             } else {
-                __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col0;
-#pragma unroll
-                for (int i = 0; i < 32; i += 8)
-                    store16B(o16 + i, pack_bf16(v[i], v[i + 1]), pack_bf16(v[i + 2], v[i + 3]),
-                             pack_bf16(v[i + 4], v[i + 5]), pack_bf16(v[i + 6], v[i + 7]));
+                __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col;
+                *reinterpret_cast<uint2*>(o16) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
             }
         }
-    } else if constexpr (EPI == EPI_LN_GELU) {
-        // two passes over the 512 accumulator columns of this row: statistics, then normalise
-        float sum = 0.f, sumsq = 0.f;
+        __syncwarp();
+    }
+}
+
+// Linear(512 -> 512) -> LayerNorm(512) -> GELU(erf): the whole row sits in TMEM (BLOCK_N = 512).
+__device__ __forceinline__ void epilogue_ln_gelu(const GemmParams& p, const EpiSmem& es, uint32_t acc_taddr,
+                                                 long long tile_row0, int quarter, int half, int lane) {
+    uint32_t r[32];
+    float sum = 0.f, sumsq = 0.f;
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 32; ++c) {
-            tmem_ld32(acc_taddr + c * 32, r);
-            tmem_ld_wait();
+    for (int c = half; c < 16; c += 2) {
+        tmem_ld32(acc_taddr + c * 32, r);
+        tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float x = __uint_as_float(r[i]) + __ldg(p.bias + c * 32 + i);
-                sum += x;
-                sumsq += x * x;
-            }
+        for (int q = 0; q < 8; ++q) {
+            const float4 b = *reinterpret_cast<const float4*>(es.bias + c * 32 + q * 4);
+            const float x0 = __uint_as_float(r[q * 4]) + b.x, x1 = __uint_as_float(r[q * 4 + 1]) + b.y;
+            const float x2 = __uint_as_float(r[q * 4 + 2]) + b.z, x3 = __uint_as_float(r[q * 4 + 3]) + b.w;
+            sum += (x0 + x1) + (x2 + x3);
+            sumsq = fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, fmaf(x3, x3, sumsq))));
         }
-        const float mean = sum * (1.0f / BLOCK_N);
-        const float var = fmaxf(sumsq * (1.0f / BLOCK_N) - mean * mean, 0.f);
-        const float rstd = rsqrtf(var + p.ln_eps);
-        __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) + row_in_batch * p.ld16;
+    }
+    const int row = quarter * 32 + lane;
+    es.exch[half * 128 + row] = make_float2(sum, sumsq);
+    epi_bar_sync();
+    const float2 other = es.exch[(half ^ 1) * 128 + row];
+    sum += other.x;
+    sumsq += other.y;
+    const float mean = sum * (1.0f / 512.f);
+    const float var = fmaxf(sumsq * (1.0f / 512.f) - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + p.ln_eps);
+    const float nmr = -mean * rstd;
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 32; ++c) {
-            tmem_ld32(acc_taddr + c * 32, r);
-            tmem_ld_wait();
-            float v[32];
+    for (int c = half; c < 16; c += 2) {
+        tmem_ld32(acc_taddr + c * 32, r);
+        tmem_ld_wait();
+        uint32_t pk[16];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int col = c * 32 + i;
-                const float x = __uint_as_float(r[i]) + __ldg(p.bias + col);
-                v[i] = gelu_erf((x - mean) * rstd * __ldg(p.ln_gamma + col) + __ldg(p.ln_beta + col));
-            }
-            if (row_valid) {
-#pragma unroll
-                for (int i = 0; i < 32; i += 8)
-                    store16B(o16 + c * 32 + i, pack_bf16(v[i], v[i + 1]), pack_bf16(v[i + 2], v[i + 3]),
-                             pack_bf16(v[i + 4], v[i + 5]), pack_bf16(v[i + 6], v[i + 7]));
-            }
+        for (int q = 0; q < 8; ++q) {
+            const int col = c * 32 + q * 4;
+            const float4 b = *reinterpret_cast<const float4*>(es.bias + col);
+            const float4 g = *reinterpret_cast<const float4*>(es.par1 + col);
+            const float4 be = *reinterpret_cast<const float4*>(es.par2 + col);
+            const float y0 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4]) + b.x, rstd, nmr), g.x, be.x));
+            const float y1 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 1]) + b.y, rstd, nmr), g.y, be.y));
+            const float y2 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 2]) + b.z, rstd, nmr), g.z, be.z));
+            const float y3 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 3]) + b.w, rstd, nmr), g.w, be.w));
+            pk[q * 2] = pack_bf16(y0, y1);
+            pk[q * 2 + 1] = pack_bf16(y2, y3);
         }
-    } else if constexpr (EPI == EPI_CONV_RELU_BN) {
+        // staging rows are 64 B (32 bf16): 16-byte chunk j of row l sits at l*64 + ((j ^ ((l >> 1) & 3)) << 4)
+        uint8_t* myrow = es.stage + lane * 64;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(myrow + ((j ^ ((lane >> 1) & 3)) << 4)) =
+                make_uint4(pk[j * 4], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int rr = it * 8 + (lane >> 2), cj = lane & 3;
+            const uint4 v = *reinterpret_cast<const uint4*>(es.stage + rr * 64 + ((cj ^ ((rr >> 1) & 3)) << 4));
+            const long long grow = tile_row0 + rr;
+            if (grow < p.M)
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + c * 32 + cj * 8) = v;
+        }
+        __syncwarp();
+    }
+    epi_bar_sync();  // exch is rewritten by the next tile
+}
+
+// thread-per-row epilogues of the SuperPoint convolutions / heads (per-column operands from smem)
+template <int BLOCK_N, int EPI>
+__device__ __forceinline__ void epilogue_conv(const GemmParams& p, const EpiSmem& es, uint32_t acc_taddr,
+                                              long long row_in_batch, bool row_valid, int half, int n0, int lane,
+                                              int img, int py, int px) {
+    uint32_t r[32];
+    if constexpr (EPI == EPI_CONV_RELU_BN) {
         // pixel (img, py, px); with pooling the 2x2 partners are lanes ^1 (x) and ^16 (y)
         const bool store_lane = p.pool ? ((lane & 17) == 0) : true;
         const int oy = p.pool ? (py >> 1) : py, ox = p.pool ? (px >> 1) : px;
@@ -157,21 +220,32 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_
         __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) +
                              (((long long)img * OH + oy) * OW + ox) * p.ld16 + n0;
 #pragma unroll 1
-        for (int c = 0; c < BLOCK_N / 32; ++c) {
+        for (int c = half; c < BLOCK_N / 32; c += 2) {
             tmem_ld32(acc_taddr + c * 32, r);
             tmem_ld_wait();
             float v[32];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int col = n0 + c * 32 + i;
-                float x = __uint_as_float(r[i]) + __ldg(p.bias + col);
-                if (p.relu) x = fmaxf(x, 0.f);
-                x = x * __ldg(p.scale + col) + __ldg(p.shift + col);
-                if (p.pool) {
+            for (int q = 0; q < 8; ++q) {
+                const int col = n0 + c * 32 + q * 4;
+                const float4 b = *reinterpret_cast<const float4*>(es.bias + col);
+                const float4 s = *reinterpret_cast<const float4*>(es.par1 + col);
+                const float4 t = *reinterpret_cast<const float4*>(es.par2 + col);
+                float x0 = __uint_as_float(r[q * 4]) + b.x, x1 = __uint_as_float(r[q * 4 + 1]) + b.y;
+                float x2 = __uint_as_float(r[q * 4 + 2]) + b.z, x3 = __uint_as_float(r[q * 4 + 3]) + b.w;
+                if (p.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f); }
+                v[q * 4] = fmaf(x0, s.x, t.x);
+                v[q * 4 + 1] = fmaf(x1, s.y, t.y);
+                v[q * 4 + 2] = fmaf(x2, s.z, t.z);
+                v[q * 4 + 3] = fmaf(x3, s.w, t.w);
+            }
+            if (p.pool) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    float x = v[i];
                     x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 1));
                     x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, 16));
+                    v[i] = x;
                 }
-                v[i] = x;
             }
             if (ok) {
 #pragma unroll
@@ -181,6 +255,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_
             }
         }
     } else if constexpr (EPI == EPI_CONV_BN_L2) {
+        if (half != 0) return;  // one warp per lane quarter keeps the whole 256-column row
         float sumsq = 0.f;
 #pragma unroll 1
         for (int c = 0; c < BLOCK_N / 32; ++c) {
@@ -189,8 +264,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
                 const int col = c * 32 + i;
-                const float x = (__uint_as_float(r[i]) + __ldg(p.bias + col)) * __ldg(p.scale + col) +
-                                __ldg(p.shift + col);
+                const float x = (__uint_as_float(r[i]) + es.bias[col]) * es.par1[col] + es.par2[col];
                 sumsq += x * x;
             }
         }
@@ -207,13 +281,13 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int col = c * 32 + i + j;
-                    v[j] = ((__uint_as_float(r[i + j]) + __ldg(p.bias + col)) * __ldg(p.scale + col) +
-                            __ldg(p.shift + col)) * inv;
+                    v[j] = ((__uint_as_float(r[i + j]) + es.bias[col]) * es.par1[col] + es.par2[col]) * inv;
                 }
                 *reinterpret_cast<float4*>(o32 + c * 32 + i) = make_float4(v[0], v[1], v[2], v[3]);
             }
         }
     } else if constexpr (EPI == EPI_CONV_BN_SOFTMAX_D2S) {
+        if (half != 0) return;
         // 65 logits per cell (columns 0..64 of an 80-wide tile)
         float v[80];
         uint32_t q[16];
@@ -232,7 +306,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t acc_
         float mx = -INFINITY;
 #pragma unroll
         for (int i = 0; i < 65; ++i) {
-            v[i] = (v[i] + __ldg(p.bias + i)) * __ldg(p.scale + i) + __ldg(p.shift + i);
+            v[i] = (v[i] + es.bias[i]) * es.par1[i] + es.par2[i];
             mx = fmaxf(mx, v[i]);
         }
         float sum = 0.f;
@@ -275,6 +349,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint64_t* acc_full = empty_bar + Cfg::kStages;
     uint64_t* acc_empty = acc_full + Cfg::kAccStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + Cfg::kAccStages);
+    float* s_par = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
+    uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_par + kParamFloats);
+    float2* s_exch = reinterpret_cast<float2*>(s_stage + kEpiWarps * kStageBytesPerWarp);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -292,7 +369,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         for (int s = 0; s < Cfg::kAccStages; ++s) {
             mbar_init(acc_full + s, 1);
-            mbar_init(acc_empty + s, 4);  // one arrival per epilogue warp
+            mbar_init(acc_empty + s, kEpiWarps);  // one arrival per epilogue warp
         }
         fence_barrier_init();
     }
@@ -371,7 +448,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
     } else {
         // ===================== epilogue warps (TMEM lanes 32*(warp%4) ..) =====================
-        const int quarter = warp & 3;
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        const int et = threadIdx.x - 64;
+        // per-column operands -> smem once per CTA
+        {
+            const float* src1 = EPI == EPI_LN_GELU ? p.ln_gamma : p.scale;
+            const float* src2 = EPI == EPI_LN_GELU ? p.ln_beta : p.shift;
+            const int n = p.N < 768 ? p.N : 768;
+            for (int i = et; i < n; i += 32 * kEpiWarps) {
+                if (p.bias != nullptr) s_par[i] = __ldg(p.bias + i);
+                if (src1 != nullptr) s_par[768 + i] = __ldg(src1 + i);
+                if (src2 != nullptr) s_par[1536 + i] = __ldg(src2 + i);
+            }
+            epi_bar_sync();
+        }
+        EpiSmem es;
+        es.bias = s_par;
+        es.par1 = s_par + 768;
+        es.par2 = s_par + 1536;
+        es.stage = s_stage + (warp - 2) * kStageBytesPerWarp;
+        es.exch = s_exch;
         const int r_in_tile = quarter * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -380,22 +476,28 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const long long rest = t / n_tiles;
             const int mt = (int)(rest % m_tiles);
             const int b = (int)(rest / m_tiles);
-            long long row_in_batch = 0;
-            bool row_valid;
-            int py = 0, px = 0;
-            if constexpr (A_MODE == 1) {
-                const int ty = mt / p.tiles_x, tx = mt - ty * p.tiles_x;
-                py = ty * kTileH + (r_in_tile >> 4);
-                px = tx * kTileW + (r_in_tile & 15);
-                row_valid = py < p.H && px < p.W;
-            } else {
-                row_in_batch = (long long)mt * kBlockM + r_in_tile;
-                row_valid = row_in_batch < p.M;
-            }
             mbar_wait(acc_full + acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + ((uint32_t)(quarter * 32) << 16);
-            epilogue_tile<BLOCK_N, EPI>(p, taddr, b, row_in_batch, row_valid, nt * BLOCK_N, lane, b, py, px);
+            if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_QKV_ROTARY || EPI == EPI_RESID || EPI == EPI_F32) {
+                epilogue_rows<BLOCK_N, EPI>(p, es, taddr, b, (long long)mt * kBlockM + quarter * 32, half, nt * BLOCK_N, lane);
+            } else if constexpr (EPI == EPI_LN_GELU) {
+                epilogue_ln_gelu(p, es, taddr, (long long)mt * kBlockM + quarter * 32, quarter, half, lane);
+            } else {
+                long long row_in_batch = 0;
+                bool row_valid;
+                int py = 0, px = 0;
+                if constexpr (A_MODE == 1) {
+                    const int ty = mt / p.tiles_x, tx = mt - ty * p.tiles_x;
+                    py = ty * kTileH + (r_in_tile >> 4);
+                    px = tx * kTileW + (r_in_tile & 15);
+                    row_valid = py < p.H && px < p.W;
+                } else {
+                    row_in_batch = (long long)mt * kBlockM + r_in_tile;
+                    row_valid = row_in_batch < p.M;
+                }
+                epilogue_conv<BLOCK_N, EPI>(p, es, taddr, row_in_batch, row_valid, half, nt * BLOCK_N, lane, b, py, px);
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty + acc);
