@@ -7,12 +7,16 @@
 //   warps 6-9   softmax group 1 (query tile 1)
 // Per 128-key tile and group g:
 //   S_g = Q_g K^T    (tcgen05.mma M=128 N=128 K=64, fp32 in TMEM)
-//   online softmax by the group's 128 threads (tcgen05.ld), P_g -> smem as bf16 (128B-swizzled, K-major)
-//   PV_g = P_g V     (tcgen05.mma M=128 N=64 K=128, V consumed token-major through an MN-major descriptor)
-//   O_g = O_g * alpha + PV_g in registers.
+//   the group's 128 threads pull their S row into registers (tcgen05.ld) and release S_g at once, so the
+//   next S_g is computed while this one is exponentiated; P_g -> smem as bf16 (128B-swizzled, K-major)
+//   O_g += P_g V     (tcgen05.mma M=128 N=64 K=128, accumulating in TMEM; V consumed token-major through
+//                     an MN-major descriptor)
+// Online softmax with a lazily updated reference maximum: the running maximum m only moves (and O_g /
+// the row sum are rescaled, tcgen05.ld -> multiply -> tcgen05.st) when a row's new maximum exceeds it by
+// more than 2^8 in the exp2 domain; otherwise P is simply taken against the stale m (values <= 256,
+// harmless for bf16 / fp32) - the final O / l is mathematically unchanged.
 // The two groups ping-pong: while one group runs its exponentials (the MUFU-bound part: 128x128 ex2 per
-// tile against 2 x 2 MFLOP of MMA), the tensor core works on the other group's S / PV, and the next
-// S_g is issued as soon as the group has consumed the previous one.
+// tile against 2 x 2 MFLOP of MMA), the tensor core works on the other group's S / PV.
 // Q/K/V tiles arrive by TMA from token-major [tokens, ld] bf16 matrices; a head is a 64-column slice.
 // The S matrix is never materialised in HBM.  Self-attention and both directions of the bidirectional
 // cross-attention use this kernel (the cross block's similarity is recomputed per direction).
@@ -54,7 +58,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     uint64_t* v_full = k_full + kKvStages;       // [kKvStages]
     uint64_t* kv_empty = v_full + kKvStages;     // [kKvStages]
     uint64_t* s_full = kv_empty + kKvStages;     // [2]
-    uint64_t* p_ready = s_full + 2;              // [2]
+    uint64_t* s_free = s_full + 2;               // [2]
+    uint64_t* p_ready = s_free + 2;              // [2]
     uint64_t* o_full = p_ready + 2;              // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
@@ -74,6 +79,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         for (int g = 0; g < 2; ++g) {
             mbar_init(q_full + g, 1);
             mbar_init(s_full + g, 1);
+            mbar_init(s_free + g, 4);
             mbar_init(p_ready + g, 4);
             mbar_init(o_full + g, 1);
         }
@@ -138,20 +144,25 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             for (int j = 0; j < kv_tiles; ++j) {
                 const int next_stage = stage + 1 == kKvStages ? 0 : stage + 1;
                 const uint32_t next_phase = stage + 1 == kKvStages ? phase ^ 1 : phase;
+                if (j + 1 < kv_tiles) {
+                    mbar_wait(k_full + next_stage, next_phase);
+                    for (int g = 0; g < groups; ++g) {
+                        mbar_wait(s_free + g, j & 1);  // the group holds S_g(j) in registers
+                        tc_fence_after();
+                        issue_s(g, next_stage);
+                    }
+                }
                 mbar_wait(v_full + stage, phase);
-                if (j + 1 < kv_tiles) mbar_wait(k_full + next_stage, next_phase);
                 for (int g = 0; g < groups; ++g) {
-                    // P_g(j) is in smem; the group has consumed S_g(j) and PV_g(j-1)
-                    mbar_wait(p_ready + g, j & 1);
+                    mbar_wait(p_ready + g, j & 1);  // P_g(j) is in smem (and O_g rescaled if it had to be)
                     tc_fence_after();
                     const uint32_t ap = smem_u32(sP + g * 2 * kTileBytes), bv = smem_u32(sV + stage * kTileBytes);
 #pragma unroll
                     for (int k = 0; k < kKvTile / 16; ++k)
                         umma_f16(tmem_base + 256 + g * 64,
                                  umma_smem_desc_sw128(ap + (k >> 2) * kTileBytes + (k & 3) * 32, 1024, 16),
-                                 umma_smem_desc_sw128(bv + k * 2048, 1024, 1024), idesc_o, k != 0 ? 1u : 0u);
+                                 umma_smem_desc_sw128(bv + k * 2048, 1024, 1024), idesc_o, (j | k) != 0 ? 1u : 0u);
                     umma_commit(o_full + g);
-                    if (j + 1 < kv_tiles) issue_s(g, next_stage);
                 }
                 umma_commit(kv_empty + stage);  // K_j / V_j are free once everything issued so far retires
                 stage = next_stage;
@@ -170,87 +181,105 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         if (g == 0 || g1_active) {
             const float c = p.scale * 1.4426950408889634f;  // softmax(scale * s) via exp2
             float m_run = -INFINITY, l_run = 0.f;
-            float o[kHeadDim];
-#pragma unroll
-            for (int i = 0; i < kHeadDim; ++i) o[i] = 0.f;
+            float sv[kKvTile];
             uint32_t r[32];
             for (int j = 0; j < kv_tiles; ++j) {
                 const int valid = min(kKvTile, kv_len - j * kKvTile);
                 mbar_wait(s_full + g, j & 1);
                 tc_fence_after();
-                // pass 1: row maximum
-                float m_new = m_run;
-#pragma unroll 1
-                for (int ch = 0; ch < 4; ++ch) {
-                    tmem_ld32(tmem_s + ch * 32, r);
-                    tmem_ld_wait();
-                    if (valid == kKvTile) {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) m_new = fmaxf(m_new, __uint_as_float(r[i]));
-                    } else {
+                for (int ch = 0; ch < 4; ++ch) B200_TMEM_LD32F(tmem_s + ch * 32, sv + ch * 32);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(s_free + g);  // S_g(j+1) may overwrite the TMEM buffer now
+                if (valid < kKvTile) {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            if (ch * 32 + i < valid) m_new = fmaxf(m_new, __uint_as_float(r[i]));
-                    }
+                    for (int i = 0; i < kKvTile; ++i)
+                        if (i >= valid) sv[i] = -INFINITY;
                 }
-                const float alpha = ex2_approx((m_run - m_new) * c);
-                const float mc = m_new * c;
-                float l_tile = 0.f;
-                // pass 2: P = exp2(s*c - m*c) -> bf16 -> swizzled smem
-#pragma unroll 1
-                for (int ch = 0; ch < 4; ++ch) {
-                    tmem_ld32(tmem_s + ch * 32, r);
-                    tmem_ld_wait();
-                    float e[32];
-                    if (valid == kKvTile) {
+                float m0 = sv[0], m1 = sv[1], m2 = sv[2], m3 = sv[3];
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            e[i] = ex2_approx(fmaf(__uint_as_float(r[i]), c, -mc));
-                            l_tile += e[i];
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const float x = ex2_approx(fmaf(__uint_as_float(r[i]), c, -mc));
-                            e[i] = (ch * 32 + i < valid) ? x : 0.f;
-                            l_tile += e[i];
-                        }
-                    }
-                    uint8_t* base = myP + (ch >> 1) * kTileBytes;
-#pragma unroll
-                    for (int q4 = 0; q4 < 4; ++q4) {  // 4 groups of 8 keys = 16 bytes each
-                        const int chunk = (ch & 1) * 4 + q4;
-                        *reinterpret_cast<uint4*>(base + ((chunk ^ (row & 7)) << 4)) =
-                            make_uint4(pack_bf16(e[q4 * 8], e[q4 * 8 + 1]), pack_bf16(e[q4 * 8 + 2], e[q4 * 8 + 3]),
-                                       pack_bf16(e[q4 * 8 + 4], e[q4 * 8 + 5]), pack_bf16(e[q4 * 8 + 6], e[q4 * 8 + 7]));
-                    }
+                for (int i = 4; i < kKvTile; i += 4) {
+                    m0 = fmaxf(m0, sv[i]); m1 = fmaxf(m1, sv[i + 1]);
+                    m2 = fmaxf(m2, sv[i + 2]); m3 = fmaxf(m3, sv[i + 3]);
                 }
-                m_run = m_new;
-                l_run = l_run * alpha + l_tile;
+                const float m_tile = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                // lazy rescale: move the reference maximum only when it is off by more than 2^8
+                const bool need = (m_tile - m_run) * c > 8.0f;  // always true for j == 0 (m_run = -inf)
+                bool waited = false;
+                if (j > 0 && __any_sync(0xffffffffu, need)) {
+                    mbar_wait(o_full + g, (j - 1) & 1);  // every PV issued so far has landed in O_g
+                    tc_fence_after();
+                    waited = true;
+                    const float m_new = need ? m_tile : m_run;
+                    const float alpha = ex2_approx((m_run - m_new) * c);
+                    l_run *= alpha;
+                    m_run = m_new;
+#pragma unroll 1
+                    for (int ch = 0; ch < 8; ++ch) {  // 8 columns at a time: S_g sits in registers meanwhile
+                        uint32_t t8[8];
+                        tmem_ld8(tmem_o + ch * 8, t8);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) t8[i] = __float_as_uint(__uint_as_float(t8[i]) * alpha);
+                        tmem_st8(tmem_o + ch * 8, t8);
+                    }
+                    tmem_st_wait();
+                } else if (j == 0) {
+                    m_run = m_tile;
+                }
+                if (j > 0 && !waited) {
+                    mbar_wait(o_full + g, (j - 1) & 1);  // PV_g(j-1) has finished reading the P buffer
+                    tc_fence_after();
+                }
+                const float mc = m_run * c;
+                float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+                for (int ch = 0; ch < 16; ++ch) {  // 16 chunks of 8 keys = 16 bytes each
+                    uint32_t pk[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float e0 = ex2_approx(fmaf(sv[ch * 8 + 2 * i], c, -mc));
+                        const float e1 = ex2_approx(fmaf(sv[ch * 8 + 2 * i + 1], c, -mc));
+                        l0 += e0;
+                        l1 += e1;
+                        pk[i] = pack_bf16(e0, e1);
+                    }
+                    uint8_t* base = myP + (ch >> 3) * kTileBytes;
+                    *reinterpret_cast<uint4*>(base + (((ch & 7) ^ (row & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                }
+                l_run += l0 + l1;
                 tc_fence_before();
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(p_ready + g);
-                // accumulate PV
-                mbar_wait(o_full + g, j & 1);
+            }
+            if (kv_tiles > 0) {
+                mbar_wait(o_full + g, (kv_tiles - 1) & 1);
                 tc_fence_after();
+            }
+            const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;  // no keys: zeros
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)(sd.q_row0 + q_idx) * p.ld_out +
+                                 p.out_col0 + head * kHeadDim;
 #pragma unroll
-                for (int ch = 0; ch < 2; ++ch) {
+            for (int ch = 0; ch < 2; ++ch) {
+                if (kv_tiles > 0) {
                     tmem_ld32(tmem_o + ch * 32, r);
                     tmem_ld_wait();
+                } else {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) o[ch * 32 + i] = fmaf(o[ch * 32 + i], alpha, __uint_as_float(r[i]));
+                    for (int i = 0; i < 32; ++i) r[i] = 0u;
                 }
-            }
-            if (q_idx < q_len) {
-                const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;  // no keys: zeros
-                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                     (long long)(sd.q_row0 + q_idx) * p.ld_out + p.out_col0 + head * kHeadDim;
+                if (q_idx < q_len) {
 #pragma unroll
-                for (int i = 0; i < kHeadDim; i += 8)
-                    *reinterpret_cast<uint4*>(dst + i) =
-                        make_uint4(pack_bf16(o[i] * inv, o[i + 1] * inv), pack_bf16(o[i + 2] * inv, o[i + 3] * inv),
-                                   pack_bf16(o[i + 4] * inv, o[i + 5] * inv), pack_bf16(o[i + 6] * inv, o[i + 7] * inv));
+                    for (int i = 0; i < 32; i += 8)
+                        *reinterpret_cast<uint4*>(dst + ch * 32 + i) = make_uint4(
+                            pack_bf16(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv),
+                            pack_bf16(__uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv),
+                            pack_bf16(__uint_as_float(r[i + 4]) * inv, __uint_as_float(r[i + 5]) * inv),
+                            pack_bf16(__uint_as_float(r[i + 6]) * inv, __uint_as_float(r[i + 7]) * inv));
+                }
             }
         }
     }
