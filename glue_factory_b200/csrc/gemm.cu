@@ -96,6 +96,24 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
             *reinterpret_cast<float4*>(myrow + ((q ^ (lane & 7)) << 4)) = v;
         }
         __syncwarp();
+        // residual / rotary operands of all 8 row groups first (out32 may alias resid: keep the loads ahead
+        // of the stores so that eight 128-byte row segments are in flight per warp)
+        float4 aux[8];
+        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const long long row_in_batch = tile_row0 + it * 4 + (lane >> 3);
+                const int col = col0 + (lane & 7) * 4;
+                aux[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row_in_batch < p.M) {
+                    const long long grow = row_base + row_in_batch;
+                    if constexpr (EPI == EPI_RESID)
+                        aux[it] = *reinterpret_cast<const float4*>(p.resid + grow * p.ld32 + col);
+                    else if (col0 < p.rot_cols)
+                        aux[it] = __ldg(reinterpret_cast<const float4*>(p.cs + grow * 32 + ((col & 63) >> 1)));
+                }
+            }
+        }
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int rr = it * 4 + (lane >> 3), cj = lane & 7;
@@ -107,7 +125,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
             if constexpr (EPI == EPI_QKV_ROTARY) {
                 if (col0 < p.rot_cols) {
                     // (cos, sin) of frequencies (col & 63) / 2 and + 1
-                    const float4 t = __ldg(reinterpret_cast<const float4*>(p.cs + grow * 32 + ((col & 63) >> 1)));
+                    const float4 t = aux[it];
                     const float x0 = v.x, x1 = v.y, x2 = v.z, x3 = v.w;
                     v.x = x0 * t.x - x1 * t.y;
                     v.y = x1 * t.x + x0 * t.y;
@@ -116,7 +134,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
                 }
             }
             if constexpr (EPI == EPI_RESID) {
-                const float4 t = *reinterpret_cast<const float4*>(p.resid + grow * p.ld32 + col);
+                const float4 t = aux[it];
                 v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
                 *reinterpret_cast<float4*>(p.out32 + grow * p.ld32 + col) = v;
             }
