@@ -9,7 +9,7 @@ LIB_PATH = os.path.join(_HERE, "libb200glue.so")
 
 EPI_BIAS_BF16, EPI_QKV_ROTARY, EPI_LN_GELU, EPI_RESID, EPI_F32 = 0, 1, 2, 3, 4
 EPI_CONV_RELU_BN, EPI_CONV_BN_L2, EPI_CONV_BN_SOFTMAX_D2S = 5, 6, 7
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class GemmDesc(C.Structure):
@@ -58,7 +58,15 @@ _SIGNATURES = {
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200_sp_nms_border": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "b200_sp_nms_border_list": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
-                                          C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "b200_sp_sample_descriptors_mode": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                                  C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "b200_sg_keypoint_encoder_head": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_sg_sinkhorn_workspace": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "b200_sg_sinkhorn_assignment": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                              C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_void_p]),
     "b200_sp_select_topk_list": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p,
                                            C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p]),

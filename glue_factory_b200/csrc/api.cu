@@ -253,10 +253,11 @@ int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius,
                        b200_stream_t stream) {
     return launch_nms_border(scores, B, H, W, nms_radius, remove_borders, out, static_cast<cudaStream_t>(stream));
 }
-int b200_sp_nms_border_list(const float* scores, int B, int H, int W, int nms_radius, int remove_borders, float* out,
-                            unsigned long long* candidates, int* candidate_state, int capacity, b200_stream_t stream) {
-    return launch_nms_list(scores, B, H, W, nms_radius, remove_borders, out, candidates, candidate_state, capacity,
-                           static_cast<cudaStream_t>(stream));
+int b200_sp_nms_border_list(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
+                            const int* image_hw, float* out, unsigned long long* candidates, int* candidate_state,
+                            int capacity, b200_stream_t stream) {
+    return launch_nms_list(scores, B, H, W, nms_radius, remove_borders, image_hw, out, candidates, candidate_state,
+                           capacity, static_cast<cudaStream_t>(stream));
 }
 int b200_sp_select_topk_list(const float* nms_map, int B, int H, int W, float threshold, int k,
                              const unsigned long long* candidates, int* candidate_state, int capacity,
@@ -275,7 +276,12 @@ int b200_sp_select_topk(const float* nms_map, int B, int H, int W, float thresho
 }
 int b200_sp_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* keypoints, int K,
                                int stride, float* out, b200_stream_t stream) {
-    return launch_sample_descriptors(dense, B, Hc, Wc, C, keypoints, K, stride, out, static_cast<cudaStream_t>(stream));
+    return launch_sample_descriptors(dense, B, Hc, Wc, C, keypoints, K, stride, 0, out, static_cast<cudaStream_t>(stream));
+}
+int b200_sp_sample_descriptors_mode(const float* dense, int B, int Hc, int Wc, int C, const float* keypoints, int K,
+                                    int stride, int mode, float* out, b200_stream_t stream) {
+    return launch_sample_descriptors(dense, B, Hc, Wc, C, keypoints, K, stride, mode, out,
+                                     static_cast<cudaStream_t>(stream));
 }
 int b200_lg_ingest(const float* desc, long long rows, float* x32, void* xm, long long ld_xm, b200_stream_t stream) {
     return launch_ingest(desc, rows, x32, xm, ld_xm, static_cast<cudaStream_t>(stream));
@@ -294,6 +300,22 @@ int b200_lg_assignment(const float* sim, const float* z0, const float* z1, int B
                        long long* matches1, float* mscores0, float* mscores1, b200_stream_t stream) {
     return launch_assignment(sim, z0, z1, B, M, N, filter_threshold, workspace, scores, matches0, matches1, mscores0,
                              mscores1, static_cast<cudaStream_t>(stream));
+}
+
+int b200_sg_keypoint_encoder_head(const float* keypoints, const float* scores, const float* image_size, int B, int n,
+                                  const float* w1, const float* b1, const float* w2, const float* b2, void* out,
+                                  b200_stream_t stream) {
+    B200_REQUIRE(keypoints && scores && image_size && w1 && b1 && w2 && b2 && out, "keypoint encoder: null argument");
+    return launch_sg_kenc_head(keypoints, scores, image_size, B, n, w1, b1, w2, b2, out, static_cast<cudaStream_t>(stream));
+}
+size_t b200_sg_sinkhorn_workspace(int B, int M, int N) { return sinkhorn_workspace_bytes(B, M, N); }
+int b200_sg_sinkhorn_assignment(const float* cost, const float* bin_score, int B, int M, int N, int iters,
+                                float filter_threshold, void* workspace, float* scores, long long* matches0,
+                                long long* matches1, float* mscores0, float* mscores1, b200_stream_t stream) {
+    B200_REQUIRE(cost && bin_score && workspace && scores && matches0 && matches1 && mscores0 && mscores1,
+                 "sinkhorn: null argument");
+    return launch_sinkhorn_assignment(cost, bin_score, B, M, N, iters, filter_threshold, workspace, scores, matches0,
+                                      matches1, mscores0, mscores1, static_cast<cudaStream_t>(stream));
 }
 
 int b200_lg_count_below(const float* conf, int n, float threshold, int* out, b200_stream_t stream) {

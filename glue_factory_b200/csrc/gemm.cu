@@ -93,6 +93,9 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
                 const float4 b = *reinterpret_cast<const float4*>(es.bias + col0 + q * 4);
                 v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
             }
+            if (EPI == EPI_BIAS_BF16 && p.relu) {
+                v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+            }
             *reinterpret_cast<float4*>(myrow + ((q ^ (lane & 7)) << 4)) = v;
         }
         __syncwarp();
@@ -555,6 +558,7 @@ int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const C
     B200_REQUIRE(p.K > 0 && p.K % kBlockK == 0, "gemm: K=%d must be a positive multiple of 64", p.K);
 #define B200_CASE(BN, E, AM) \
     if (block_n == BN && epi == E && a_mode == AM) return launch_one<BN, E, AM>(ta, tb, p, num_sms, stream);
+    B200_CASE(128, EPI_BIAS_BF16, 0)
     B200_CASE(256, EPI_BIAS_BF16, 0)
     B200_CASE(256, EPI_QKV_ROTARY, 0)
     B200_CASE(512, EPI_LN_GELU, 0)

@@ -6,7 +6,7 @@
 namespace b200 {
 
 enum EpiKind : int {
-    EPI_BIAS_BF16 = 0,           // out16[row, col] = acc + bias
+    EPI_BIAS_BF16 = 0,           // out16[row, col] = acc + bias (ReLU when relu != 0)
     EPI_QKV_ROTARY = 1,          // as above, rotary embedding on columns < rot_cols
     EPI_LN_GELU = 2,             // bias -> LayerNorm(512) -> GELU(erf) -> out16   (BLOCK_N == N == 512)
     EPI_RESID = 3,               // out32 = acc + bias + resid ; out16 = bf16(out32)

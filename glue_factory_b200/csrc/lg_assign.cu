@@ -128,8 +128,8 @@ __global__ void __launch_bounds__(256) assign_combine_kernel(int M, int N, int t
 }
 
 // pass 2: write the scores, track per-tile row / column maxima (lowest index wins ties)
-__global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __restrict__ sim, int M, int N, AssignWs w,
-                                                              float* __restrict__ scores) {
+__global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __restrict__ sim, float simw, int M, int N,
+                                                              AssignWs w, float* __restrict__ scores) {
     __shared__ float2 srow[kATileM][8];
     const int b = blockIdx.z, tm = blockIdx.y, tn = blockIdx.x;
     const int tiles_n = gridDim.x, tiles_m = gridDim.y;
@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __res
         const int i = tm * kATileM + r;
         float v = -INFINITY;
         if (col_ok && i < M) {
-            v = 2.f * base[(long long)i * N + j] + w.rowterm[(long long)b * M + i] + ct;
+            v = simw * base[(long long)i * N + j] + w.rowterm[(long long)b * M + i] + ct;
             sc[(long long)i * (N + 1) + j] = v;
             if (v > cbest) { cbest = v; cidx = i; }
         }
@@ -231,11 +231,28 @@ int launch_assignment(const float* sim, const float* z0, const float* z1, int B,
     dim3 tiles(tn, tm, B), lin((M + N + 1 + 255) / 256, B);
     assign_stats_kernel<<<tiles, 256, 0, stream>>>(sim, M, N, w);
     assign_combine_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, z0, z1, w, scores);
-    assign_finalize_kernel<<<tiles, 256, 0, stream>>>(sim, M, N, w, scores);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return launch_assignment_finalize(sim, 2.0f, B, M, N, threshold, workspace, scores, m0, m1, ms0, ms1, stream);
+}
+
+// scores[:M,:N] = simw * sim + rowterm + colterm (terms in the workspace), then arg-max + mutual-NN filter
+int launch_assignment_finalize(const float* sim, float simw, int B, int M, int N, float threshold, void* workspace,
+                               float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
+                               cudaStream_t stream) {
+    const AssignWs w = carve(workspace, B, M, N);
+    const int tn = (N + kATileN - 1) / kATileN, tm = (M + kATileM - 1) / kATileM;
+    dim3 tiles(tn, tm, B), lin((M + N + 1 + 255) / 256, B);
+    assign_finalize_kernel<<<tiles, 256, 0, stream>>>(sim, simw, M, N, w, scores);
     assign_argmax_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, w);
     filter_matches_kernel<<<lin, 256, 0, stream>>>(M, N, threshold, w, m0, m1, ms0, ms1);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+void assignment_terms(void* workspace, int B, int M, int N, float** rowterm, float** colterm) {
+    const AssignWs w = carve(workspace, B, M, N);
+    *rowterm = w.rowterm;
+    *colterm = w.colterm;
 }
 
 }  // namespace b200

@@ -1,0 +1,62 @@
+// SuperGlue keypoint encoder, first two layers on the CUDA cores (K = 3 and K = 32 are too small for the
+// tensor cores): normalise (x, y) by the image size, append the detection score, then
+//   Conv1d(3 -> 32) + BatchNorm1d + ReLU -> Conv1d(32 -> 64) + BatchNorm1d + ReLU
+// with the (eval-mode) batch norms folded into the weights on the host.  Output: bf16 [tokens, 64], the
+// A operand of the remaining encoder layers, which run on the tcgen05 GEMM path.
+// (reference: gluefactory_nonfree/superglue.py:63-102,279-288)
+#include "common.cuh"
+#include "lg_kernels.cuh"
+
+namespace b200 {
+
+__global__ void __launch_bounds__(256) sg_kenc_head_kernel(const float* __restrict__ kpts, const float* __restrict__ scores,
+                                                           const float* __restrict__ size, int n, long long total,
+                                                           const float* __restrict__ w1, const float* __restrict__ b1,
+                                                           const float* __restrict__ w2, const float* __restrict__ b2,
+                                                           __nv_bfloat16* __restrict__ out) {
+    __shared__ float sw1[32 * 3], sb1[32], sw2[64 * 32], sb2[64];
+    for (int i = threadIdx.x; i < 96; i += 256) sw1[i] = w1[i];
+    for (int i = threadIdx.x; i < 32; i += 256) sb1[i] = b1[i];
+    for (int i = threadIdx.x; i < 2048; i += 256) sw2[i] = w2[i];
+    for (int i = threadIdx.x; i < 64; i += 256) sb2[i] = b2[i];
+    __syncthreads();
+    const long long t = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (t >= total) return;
+    const int b = (int)(t / n);
+    const float sw = size[2 * b], sh = size[2 * b + 1];
+    const float scale = fmaxf(sw, sh) * 0.7f;
+    // (kpts - size / 2) / (max(size) * 0.7)
+    const float x = (kpts[2 * t] - sw / 2.f) / scale, y = (kpts[2 * t + 1] - sh / 2.f) / scale;
+    const float s = scores[t];
+    float h1[32];
+#pragma unroll
+    for (int o = 0; o < 32; ++o)
+        h1[o] = fmaxf(fmaf(sw1[o * 3 + 2], s, fmaf(sw1[o * 3 + 1], y, fmaf(sw1[o * 3], x, sb1[o]))), 0.f);
+    __nv_bfloat16* dst = out + t * 64;
+#pragma unroll 1
+    for (int o0 = 0; o0 < 64; o0 += 8) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float* wr = sw2 + (o0 + j) * 32;
+            float a = sb2[o0 + j];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) a = fmaf(wr[k], h1[k], a);
+            v[j] = fmaxf(a, 0.f);
+        }
+        *reinterpret_cast<uint4*>(dst + o0) =
+            make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    }
+}
+
+int launch_sg_kenc_head(const float* kpts, const float* scores, const float* size, int B, int n, const float* w1,
+                        const float* b1, const float* w2, const float* b2, void* out, cudaStream_t stream) {
+    const long long total = (long long)B * n;
+    if (total == 0) return 0;
+    sg_kenc_head_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(kpts, scores, size, n, total, w1, b1, w2, b2,
+                                                                            reinterpret_cast<__nv_bfloat16*>(out));
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace b200

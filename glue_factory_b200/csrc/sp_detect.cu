@@ -144,8 +144,8 @@ __device__ __forceinline__ void dilate(const uint32_t* __restrict__ mask, uint32
 
 template <int R>
 __global__ void __launch_bounds__(kNmsFastThreads, 2)
-nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, float* __restrict__ out,
-                unsigned long long* __restrict__ cand, int* __restrict__ cand_count, int cap) {
+nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const int* __restrict__ image_hw,
+                float* __restrict__ out, unsigned long long* __restrict__ cand, int* __restrict__ cand_count, int cap) {
     using G = NmsGeom<R>;
     extern __shared__ uint8_t nms_fast_smem[];
     float* s = reinterpret_cast<float*>(nms_fast_smem);
@@ -185,6 +185,8 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, float* 
     }
 
     const int lane = tid & 31;
+    // bottom / right border from the per-image valid size when given (gluefactory_nonfree/superpoint.py:244-254)
+    const int bh = image_hw ? image_hw[2 * b] : H, bw = image_hw ? image_hw[2 * b + 1] : W;
     float* dst = out + (long long)b * H * W;
     unsigned long long* list = cand ? cand + (long long)b * cap : nullptr;
     // one warp per output row segment of 32 columns
@@ -200,7 +202,7 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, float* 
             const bool mx = (mask[(ey + R) * kMaskWords + 1 + (ex >> 5)] >> (ex & 31)) & 1u;
             const float sv = s[ey * G::kPitchS + R + ex];
             v = mx ? sv : 0.f;
-            const bool border = pad > 0 && (y < pad || x < pad || y >= H - pad || x >= W - pad);
+            const bool border = pad > 0 && (y < pad || x < pad || y >= bh - pad || x >= bw - pad);
             if (border) v = -1.f;
             dst[(long long)y * W + x] = v;
             keep = v > 0.f;
@@ -221,8 +223,8 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, float* 
 }
 
 template <int R>
-static int launch_nms_fast(const float* scores, int B, int H, int W, int pad, float* out, unsigned long long* cand,
-                           int* cand_count, int cap, cudaStream_t stream) {
+static int launch_nms_fast(const float* scores, int B, int H, int W, int pad, const int* image_hw, float* out,
+                           unsigned long long* cand, int* cand_count, int cap, cudaStream_t stream) {
     using G = NmsGeom<R>;
     auto kern = nms_list_kernel<R>;
     static bool configured = false;
@@ -231,14 +233,14 @@ static int launch_nms_fast(const float* scores, int B, int H, int W, int pad, fl
         configured = true;
     }
     dim3 grid((W + G::kTileW - 1) / G::kTileW, (H + G::kTileH - 1) / G::kTileH, B);
-    kern<<<grid, kNmsFastThreads, G::kSmemBytes, stream>>>(scores, H, W, pad, out, cand, cand_count, cap);
+    kern<<<grid, kNmsFastThreads, G::kSmemBytes, stream>>>(scores, H, W, pad, image_hw, out, cand, cand_count, cap);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
 
 bool nms_fast_supported(int radius) { return radius >= 1 && radius <= 4; }
 
-int launch_nms_list(const float* scores, int B, int H, int W, int radius, int pad, float* out,
+int launch_nms_list(const float* scores, int B, int H, int W, int radius, int pad, const int* image_hw, float* out,
                     unsigned long long* cand, int* cand_count, int cap, cudaStream_t stream) {
     B200_REQUIRE(nms_fast_supported(radius), "nms (list variant): radius %d outside [1, 4]", radius);
     B200_REQUIRE((long long)H * W < (1ll << 31), "nms: image too large");
@@ -248,10 +250,10 @@ int launch_nms_list(const float* scores, int B, int H, int W, int radius, int pa
         B200_CHECK_CUDA(cudaMemsetAsync(cand_count, 0, sizeof(int) * 2 * B, stream));
     }
     switch (radius) {
-        case 1: return launch_nms_fast<1>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
-        case 2: return launch_nms_fast<2>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
-        case 3: return launch_nms_fast<3>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
-        default: return launch_nms_fast<4>(scores, B, H, W, pad, out, cand, cand_count, cap, stream);
+        case 1: return launch_nms_fast<1>(scores, B, H, W, pad, image_hw, out, cand, cand_count, cap, stream);
+        case 2: return launch_nms_fast<2>(scores, B, H, W, pad, image_hw, out, cand, cand_count, cap, stream);
+        case 3: return launch_nms_fast<3>(scores, B, H, W, pad, image_hw, out, cand, cand_count, cap, stream);
+        default: return launch_nms_fast<4>(scores, B, H, W, pad, image_hw, out, cand, cand_count, cap, stream);
     }
 }
 

@@ -13,7 +13,7 @@ int launch_select_topk_flagged(const float* nms_map, int B, int H, int W, float 
                                float* kscores, int* kidx, int* counts, const int* only_flagged, cudaStream_t stream);
 // fast path (sp_detect.cu): NMS radius 1..4 with a compact list of surviving maxima, top-k over the list
 bool nms_fast_supported(int radius);
-int launch_nms_list(const float* scores, int B, int H, int W, int radius, int pad, float* out,
+int launch_nms_list(const float* scores, int B, int H, int W, int radius, int pad, const int* image_hw, float* out,
                     unsigned long long* cand, int* cand_count /*[2B]*/, int cap, cudaStream_t stream);
 int launch_select_list(const float* nms_map, int B, int H, int W, float threshold, int k,
                        const unsigned long long* cand, int* cand_count, int cap, float* kpts, float* kscores,
@@ -21,5 +21,5 @@ int launch_select_list(const float* nms_map, int B, int H, int W, float threshol
 int launch_count_candidates(const float* nms_map, int B, int H, int W, float threshold, int* counts,
                             cudaStream_t stream);
 int launch_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* kpts, int K,
-                              int stride_px, float* out, cudaStream_t stream);
+                              int stride_px, int mode, float* out, cudaStream_t stream);
 }  // namespace b200

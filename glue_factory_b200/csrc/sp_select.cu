@@ -224,15 +224,31 @@ int launch_select_topk(const float* nms_map, int B, int H, int W, float threshol
 // =============================================================================================
 __global__ void __launch_bounds__(256) sample_descriptors_kernel(const float* __restrict__ dense, int Hc, int Wc,
                                                                  int C, const float* __restrict__ kpts, int K,
-                                                                 int total, float stride_px, float* __restrict__ out) {
+                                                                 int total, float stride_px, int mode,
+                                                                 float* __restrict__ out) {
     const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (gw >= total) return;
     const int b = gw / K;
     // keypoints hold (x + 0.5, y + 0.5) in pixels of the full-resolution image
     const float kx = kpts[(long long)gw * 2], ky = kpts[(long long)gw * 2 + 1];
     // reference: g = (kp + 0.5) / ([w, h] * s) * 2 - 1 ; grid_sample unnormalises with ((g + 1) * size - 1) / 2
-    const float gx = kx / (Wc * stride_px) * 2.f - 1.f, gy = ky / (Hc * stride_px) * 2.f - 1.f;
-    const float ix = ((gx + 1.f) * Wc - 1.f) * 0.5f, iy = ((gy + 1.f) * Hc - 1.f) * 0.5f;
+    float ix, iy;
+    if (mode == 2) {
+        // MagicLeap legacy sampling (gluefactory_nonfree/superpoint.py:117-133): integer keypoint k = kp - 0.5,
+        // g = (k - s/2 + 0.5) / (w*s - s/2 - 0.5) * 2 - 1, grid_sample(align_corners=True)
+        const float hs = stride_px * 0.5f;
+        const float gx = (kx - 0.5f - hs + 0.5f) / (Wc * stride_px - hs - 0.5f) * 2.f - 1.f;
+        const float gy = (ky - 0.5f - hs + 0.5f) / (Hc * stride_px - hs - 0.5f) * 2.f - 1.f;
+        ix = (gx + 1.f) * 0.5f * (Wc - 1);
+        iy = (gy + 1.f) * 0.5f * (Hc - 1);
+    } else {
+        // mode 0: SuperPoint-open, g = (k + 0.5) / (w*s) (the keypoints passed in already hold k + 0.5);
+        // mode 1: nonfree "fix_sampling" (:138-149), g = k / (w*s); both align_corners=False
+        const float ox = mode == 1 ? kx - 0.5f : kx, oy = mode == 1 ? ky - 0.5f : ky;
+        const float gx = ox / (Wc * stride_px) * 2.f - 1.f, gy = oy / (Hc * stride_px) * 2.f - 1.f;
+        ix = ((gx + 1.f) * Wc - 1.f) * 0.5f;
+        iy = ((gy + 1.f) * Hc - 1.f) * 0.5f;
+    }
     const float fx = floorf(ix), fy = floorf(iy);
     const int x0 = (int)fx, y0 = (int)fy;
     const float wx1 = ix - fx, wy1 = iy - fy, wx0 = 1.f - wx1, wy0 = 1.f - wy1;
@@ -266,12 +282,13 @@ __global__ void __launch_bounds__(256) sample_descriptors_kernel(const float* __
 }
 
 int launch_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* kpts, int K,
-                              int stride_px, float* out, cudaStream_t stream) {
+                              int stride_px, int mode, float* out, cudaStream_t stream) {
+    B200_REQUIRE(mode >= 0 && mode <= 2, "sample_descriptors: mode %d outside [0, 2]", mode);
     B200_REQUIRE(C == 256, "sample_descriptors: descriptor_dim must be 256, got %d", C);
     const int total = B * K;
     if (total == 0) return 0;
     const int blocks = (total * 32 + 255) / 256;
-    sample_descriptors_kernel<<<blocks, 256, 0, stream>>>(dense, Hc, Wc, C, kpts, K, total, (float)stride_px, out);
+    sample_descriptors_kernel<<<blocks, 256, 0, stream>>>(dense, Hc, Wc, C, kpts, K, total, (float)stride_px, mode, out);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

@@ -224,6 +224,96 @@ def lightglue_state_dict(
     return sd
 
 
+def superpoint_nonfree_state_dict(seed: int = 0, detector_gain: float = 2.0) -> "OrderedDict[str, torch.Tensor]":
+    """Conditioned MagicLeap-SuperPoint weights (conv -> ReLU, no batch norm), 24 tensors with the
+    reference's key names (reference: gluefactory_nonfree/superpoint.py:175-196)."""
+    rng = np.random.default_rng(3000 + seed)
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+
+    def conv(name, c_in, c_out, k, gain):
+        sd[f"{name}.weight"] = _normal(rng, (c_out, c_in, k, k), gain / math.sqrt(c_in * k * k))
+        sd[f"{name}.bias"] = _normal(rng, (c_out,), 0.02)
+
+    g = math.sqrt(2.0)
+    conv("conv1a", 1, 64, 3, 2.0 * g)  # images live in [0, 1]: lift the first layer
+    conv("conv1b", 64, 64, 3, g)
+    conv("conv2a", 64, 64, 3, g)
+    conv("conv2b", 64, 64, 3, g)
+    conv("conv3a", 64, 128, 3, g)
+    conv("conv3b", 128, 128, 3, g)
+    conv("conv4a", 128, 128, 3, g)
+    conv("conv4b", 128, 128, 3, g)
+    conv("convPa", 128, 256, 3, g)
+    conv("convPb", 256, 65, 1, 1.0)  # rescaled below to a logit std of `detector_gain`
+    conv("convDa", 128, 256, 3, g)
+    conv("convDb", 256, 256, 1, 1.0)
+    # Without batch norm the all-positive ReLU features share a large common component, which makes every
+    # descriptor nearly parallel.  Centre the descriptor head on a small calibration set (float64, snapped
+    # to a 2^-20 grid so the fp32 result does not depend on the host), and scale the detector logits.
+    calib = torch.stack([synthetic_image(900 + i, 96, 96) for i in range(4)]).to(torch.float64)
+    x = calib
+    for stage, names in enumerate((("conv1a", "conv1b"), ("conv2a", "conv2b"), ("conv3a", "conv3b"), ("conv4a", "conv4b"))):
+        for n in names:
+            x = F.relu(F.conv2d(x, sd[f"{n}.weight"].double(), sd[f"{n}.bias"].double(), padding=1))
+        if stage < 3:
+            x = F.max_pool2d(x, 2, 2)
+    grid = float(1 << 20)
+    d = F.conv2d(F.relu(F.conv2d(x, sd["convDa.weight"].double(), sd["convDa.bias"].double(), padding=1)),
+                 sd["convDb.weight"].double())
+    sd["convDb.bias"] = (-torch.round(d.mean((0, 2, 3)) * grid) / grid).to(torch.float32)
+    pa = F.relu(F.conv2d(x, sd["convPa.weight"].double(), sd["convPa.bias"].double(), padding=1))
+    logits = F.conv2d(pa, sd["convPb.weight"].double())
+    std = float(torch.round(logits.std() * 1024) / 1024)
+    sd["convPb.weight"] = (sd["convPb.weight"].double() * (detector_gain / std)).to(torch.float32)
+    sd["convPb.bias"] = (-torch.round(logits.mean((0, 2, 3)) * (detector_gain / std) * grid) / grid).to(torch.float32)
+    return sd
+
+
+def superglue_state_dict(
+    seed: int = 0,
+    n_layers: int = 18,
+    dim: int = 256,
+    qk_gain: float = 12.0,
+    final_gain: float = 12.0,
+    mlp_out_gain: float = 0.02,
+    bin_score: float = 1.0,
+) -> "OrderedDict[str, torch.Tensor]":
+    """Conditioned SuperGlue weights with the reference's key names and Conv1d shapes
+    (reference: gluefactory_nonfree/superglue.py:63-72,89-140,230-245)."""
+    rng = np.random.default_rng(4000 + seed)
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+
+    def conv1d(name, c_out, c_in, gain=1.0, bias_std=0.02):
+        sd[f"{name}.weight"] = _normal(rng, (c_out, c_in, 1), gain / math.sqrt(c_in))
+        sd[f"{name}.bias"] = _normal(rng, (c_out,), bias_std) if bias_std > 0 else torch.zeros(c_out)
+
+    def bn1d(name, c):
+        sd[f"{name}.weight"] = torch.ones(c) + _normal(rng, (c,), 0.05)
+        sd[f"{name}.bias"] = _normal(rng, (c,), 0.05)
+        sd[f"{name}.running_mean"] = _normal(rng, (c,), 0.05)
+        sd[f"{name}.running_var"] = torch.ones(c) + _uniform(rng, (c,), -0.2, 0.2).to(torch.float32)
+        sd[f"{name}.num_batches_tracked"] = torch.tensor(0, dtype=torch.long)
+
+    chans = [3, 32, 64, 128, 256, dim]
+    for i in range(1, len(chans)):
+        last = i == len(chans) - 1
+        conv1d(f"kenc.encoder.{3 * (i - 1)}", chans[i], chans[i - 1], 0.25 if last else math.sqrt(2.0), 0.0 if last else 0.02)
+        if not last:
+            bn1d(f"kenc.encoder.{3 * (i - 1) + 1}", chans[i])
+    for i in range(n_layers):
+        p = f"gnn.layers.{i}"
+        conv1d(f"{p}.attn.merge", dim, dim)
+        conv1d(f"{p}.attn.proj.0", dim, dim, qk_gain)
+        conv1d(f"{p}.attn.proj.1", dim, dim, qk_gain)
+        conv1d(f"{p}.attn.proj.2", dim, dim)
+        conv1d(f"{p}.mlp.0", 2 * dim, 2 * dim, math.sqrt(2.0))
+        bn1d(f"{p}.mlp.1", 2 * dim)
+        conv1d(f"{p}.mlp.3", dim, 2 * dim, mlp_out_gain, 0.0)
+    conv1d("final_proj", dim, dim, final_gain)
+    sd["bin_score"] = torch.tensor(float(bin_score))
+    return sd
+
+
 def state_dict_sha256(sd) -> str:
     h = hashlib.sha256()
     for key, value in sd.items():

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 2
+#define B200_ABI_VERSION 3
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -112,9 +112,11 @@ int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius,
  * key << 32 | ~linear index), counted in candidate_state[0..B) (candidate_state has 2*B ints and is
  * zeroed by the call); b200_sp_select_topk_list then selects from the list, and re-does from the full map
  * only the images whose list cannot decide the result (overflow, or zero-score pixels among the top k). */
+/* image_hw: optional DEVICE array [B][2] = (h, w) of the valid image region: the bottom / right border is
+ * then taken from it per image (gluefactory_nonfree/superpoint.py:244-254); NULL = the full map. */
 int b200_sp_nms_border_list(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
-                            float* out, unsigned long long* candidates, int* candidate_state, int capacity,
-                            b200_stream_t stream);
+                            const int* image_hw, float* out, unsigned long long* candidates, int* candidate_state,
+                            int capacity, b200_stream_t stream);
 int b200_sp_select_topk_list(const float* nms_map, int B, int H, int W, float threshold, int k,
                              const unsigned long long* candidates, int* candidate_state, int capacity,
                              float* keypoints, float* scores, int* indices, int* counts, b200_stream_t stream);
@@ -130,6 +132,12 @@ int b200_sp_select_topk(const float* nms_map, int B, int H, int W, float thresho
 /* sample_descriptors (:20-31): dense is NHWC fp32 [B,Hc,Wc,256]; out [B,K,256] */
 int b200_sp_sample_descriptors(const float* dense, int B, int Hc, int Wc, int C, const float* keypoints,
                                int K, int stride, float* out, b200_stream_t stream);
+
+/* same with the grid convention selectable: mode 0 = SuperPoint-open (above), 1 = gluefactory_nonfree
+ * sample_descriptors_fix_sampling (superpoint.py:138-149), 2 = its legacy sampling, align_corners=True
+ * (superpoint.py:117-133).  keypoints always hold (x + 0.5, y + 0.5). */
+int b200_sp_sample_descriptors_mode(const float* dense, int B, int Hc, int Wc, int C, const float* keypoints,
+                                    int K, int stride, int mode, float* out, b200_stream_t stream);
 
 /* ---- LightGlue bandwidth kernels (lightglue.py) ---------------------------------------------- */
 /* fp32 descriptors -> fp32 residual stream x32 [rows,256] and bf16 copy xm[:, :256] (ld_xm elements) */
@@ -149,6 +157,20 @@ int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, 
                        float* scores /*[B,M+1,N+1]*/, long long* matches0, long long* matches1,
                        float* mscores0, float* mscores1, b200_stream_t stream);
 
+
+/* ---- SuperGlue configuration (gluefactory_nonfree/superglue.py) ------------------------------- */
+/* normalize_keypoints (:75-86) + the first two KeypointEncoder layers (:89-102) with folded BatchNorm1d:
+ * relu(W2 . relu(W1 . (x, y, score) + b1) + b2) -> bf16 [B*n, 64].  image_size [B,2] = (w, h). */
+int b200_sg_keypoint_encoder_head(const float* keypoints, const float* scores, const float* image_size, int B, int n,
+                                  const float* w1 /*[32,3]*/, const float* b1, const float* w2 /*[64,32]*/,
+                                  const float* b2, void* out, b200_stream_t stream);
+/* log_optimal_transport (:173-201) on cost [B,M,N] with the dustbin score *bin_score (device scalar),
+ * `iters` Sinkhorn iterations in one persistent cooperative kernel, then the mutual-NN filter (:288-298).
+ * scores [B,M+1,N+1]; matches int64, -1 = unmatched.  Precondition: |cost| < ~60 (fp32 exp range). */
+size_t b200_sg_sinkhorn_workspace(int B, int M, int N);
+int b200_sg_sinkhorn_assignment(const float* cost, const float* bin_score, int B, int M, int N, int iters,
+                                float filter_threshold, void* workspace, float* scores, long long* matches0,
+                                long long* matches1, float* mscores0, float* mscores1, b200_stream_t stream);
 
 /* ---- adaptive depth / width (batch size 1; lightglue.py:470-511,527-552) ---------------------- */
 /* check_if_stop: *out = number of entries of conf[0..n) below `threshold` (out is zeroed first) */
