@@ -63,6 +63,7 @@ _SIGNATURES = {
                                                   C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "b200_sg_keypoint_encoder_head": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_sg_split_hilo": (C.c_int, [C.c_void_p, C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p]),
     "b200_sg_sinkhorn_workspace": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "b200_sg_sinkhorn_assignment": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

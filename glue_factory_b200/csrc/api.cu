@@ -308,6 +308,10 @@ int b200_sg_keypoint_encoder_head(const float* keypoints, const float* scores, c
     B200_REQUIRE(keypoints && scores && image_size && w1 && b1 && w2 && b2 && out, "keypoint encoder: null argument");
     return launch_sg_kenc_head(keypoints, scores, image_size, B, n, w1, b1, w2, b2, out, static_cast<cudaStream_t>(stream));
 }
+int b200_sg_split_hilo(const float* x, long long rows, long long split_row, void* out, b200_stream_t stream) {
+    B200_REQUIRE(x && out, "split_hilo: null argument");
+    return launch_sg_split_hilo(x, rows, split_row, out, static_cast<cudaStream_t>(stream));
+}
 size_t b200_sg_sinkhorn_workspace(int B, int M, int N) { return sinkhorn_workspace_bytes(B, M, N); }
 int b200_sg_sinkhorn_assignment(const float* cost, const float* bin_score, int B, int M, int N, int iters,
                                 float filter_threshold, void* workspace, float* scores, long long* matches0,

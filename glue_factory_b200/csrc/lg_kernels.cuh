@@ -24,6 +24,7 @@ int launch_sinkhorn_assignment(const float* cost, const float* bin_score, int B,
                                float* ms0, float* ms1, cudaStream_t stream);
 int launch_sg_kenc_head(const float* kpts, const float* scores, const float* size, int B, int n, const float* w1,
                         const float* b1, const float* w2, const float* b2, void* out, cudaStream_t stream);
+int launch_sg_split_hilo(const float* x, long long rows, long long split_row, void* out, cudaStream_t stream);
 int launch_count_below(const float* conf, int n, float thr, int* out, cudaStream_t stream);
 int launch_prune(const float* match, const float* conf, int n0, int n1, float match_thr, float conf_thr, int* pos,
                  int* counts, const float* x_src, float* x_dst, const void* xm_src, void* xm_dst, long long ld_xm,

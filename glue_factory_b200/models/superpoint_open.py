@@ -48,6 +48,40 @@ def _pack_conv(conv):
     return w.permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(torch.bfloat16).contiguous()
 
 
+def sp_dense_forward(P, image):
+    """Shared dense path of both SuperPoint variants on packed weights `P` (see SuperPoint._pack):
+    image (B,1|3,H,W) fp32 -> heat map (B,8h,8w) fp32, dense descriptors NHWC (B,h,w,256) fp32."""
+    if not image.is_cuda:
+        raise RuntimeError("glue_factory_b200 SuperPoint runs on CUDA only (no CPU fallback)")
+    image = image.float().contiguous()
+    B, _, H, W = image.shape
+    dev = image.device
+    x = torch.empty(B, H, W, 64, dtype=torch.bfloat16, device=dev)
+    ops.sp_conv1a(image, P["c1a_w"], P["c1a_b"], P["c1a_s"], P["c1a_t"], x)
+    h, w = H, W
+    for L in P["convs"]:
+        oh, ow = (h // 2, w // 2) if L["pool"] else (h, w)
+        y = torch.empty(B, oh, ow, L["cout"], dtype=torch.bfloat16, device=dev)
+        ops.gemm(x, L["w"], M=0, N=L["cout"], K=9 * L["cin"], lda=L["cin"], block_n=min(L["cout"], 256),
+                 epilogue=ops.EPI_CONV_RELU_BN, batch=B, conv=(h, w, L["cin"]), bias=L["b"], scale=L["s"],
+                 shift=L["t"], relu=1, pool=L["pool"], out16=y, ld16=L["cout"])
+        x, h, w = y, oh, ow
+    heads = torch.empty(B, h, w, 512, dtype=torch.bfloat16, device=dev)
+    ops.gemm(x, P["head_w"], M=0, N=512, K=9 * 128, lda=128, block_n=256, epilogue=ops.EPI_CONV_RELU_BN,
+             batch=B, conv=(h, w, 128), bias=P["head_b"], scale=P["head_s"], shift=P["head_t"], relu=1, pool=0,
+             out16=heads, ld16=512)
+    cells = B * h * w
+    heat = torch.empty(B, h * 8, w * 8, dtype=torch.float32, device=dev)
+    ops.gemm(heads, P["det_w"], M=cells, N=65, K=256, lda=512, a_col0=0, block_n=80,
+             epilogue=ops.EPI_CONV_BN_SOFTMAX_D2S, bias=P["det_b"], scale=P["det_s"], shift=P["det_t"],
+             out32=heat, cells=(h, w))
+    dense = torch.empty(B, h, w, 256, dtype=torch.float32, device=dev)
+    ops.gemm(heads, P["desc_w"], M=cells, N=256, K=256, lda=512, a_col0=256, block_n=256,
+             epilogue=ops.EPI_CONV_BN_L2, bias=P["desc_b"], scale=P["desc_s"], shift=P["desc_t"],
+             out32=dense, ld32=256)
+    return heat, dense
+
+
 class SuperPoint(BaseModel):
     default_conf = {
         "descriptor_dim": 256,
@@ -128,36 +162,7 @@ class SuperPoint(BaseModel):
     # -- stages (also used one by one by the teacher-forced tests) ---------------------------------
     def dense_forward(self, image):
         """image (B,1|3,H,W) fp32 -> heat map (B,8h,8w) fp32, dense descriptors NHWC (B,h,w,256) fp32."""
-        if not image.is_cuda:
-            raise RuntimeError("glue_factory_b200 SuperPoint runs on CUDA only (no CPU fallback)")
-        P = self._pack()
-        image = image.float().contiguous()
-        B, _, H, W = image.shape
-        dev = image.device
-        x = torch.empty(B, H, W, 64, dtype=torch.bfloat16, device=dev)
-        ops.sp_conv1a(image, P["c1a_w"], P["c1a_b"], P["c1a_s"], P["c1a_t"], x)
-        h, w = H, W
-        for L in P["convs"]:
-            oh, ow = (h // 2, w // 2) if L["pool"] else (h, w)
-            y = torch.empty(B, oh, ow, L["cout"], dtype=torch.bfloat16, device=dev)
-            ops.gemm(x, L["w"], M=0, N=L["cout"], K=9 * L["cin"], lda=L["cin"], block_n=min(L["cout"], 256),
-                     epilogue=ops.EPI_CONV_RELU_BN, batch=B, conv=(h, w, L["cin"]), bias=L["b"], scale=L["s"],
-                     shift=L["t"], relu=1, pool=L["pool"], out16=y, ld16=L["cout"])
-            x, h, w = y, oh, ow
-        heads = torch.empty(B, h, w, 512, dtype=torch.bfloat16, device=dev)
-        ops.gemm(x, P["head_w"], M=0, N=512, K=9 * 128, lda=128, block_n=256, epilogue=ops.EPI_CONV_RELU_BN,
-                 batch=B, conv=(h, w, 128), bias=P["head_b"], scale=P["head_s"], shift=P["head_t"], relu=1, pool=0,
-                 out16=heads, ld16=512)
-        cells = B * h * w
-        heat = torch.empty(B, h * 8, w * 8, dtype=torch.float32, device=dev)
-        ops.gemm(heads, P["det_w"], M=cells, N=65, K=256, lda=512, a_col0=0, block_n=80,
-                 epilogue=ops.EPI_CONV_BN_SOFTMAX_D2S, bias=P["det_b"], scale=P["det_s"], shift=P["det_t"],
-                 out32=heat, cells=(h, w))
-        dense = torch.empty(B, h, w, 256, dtype=torch.float32, device=dev)
-        ops.gemm(heads, P["desc_w"], M=cells, N=256, K=256, lda=512, a_col0=256, block_n=256,
-                 epilogue=ops.EPI_CONV_BN_L2, bias=P["desc_b"], scale=P["desc_s"], shift=P["desc_t"],
-                 out32=dense, ld32=256)
-        return heat, dense
+        return sp_dense_forward(self._pack(), image)
 
     def detect(self, heat):
         """heat map -> (keypoints (B,K,2) incl. +0.5, scores (B,K), counts (B,) int32 on device)."""

@@ -149,8 +149,9 @@ def sp_nms_border(scores, radius, pad):
 CANDIDATE_CAPACITY = 1 << 16  # surviving maxima kept per image by the fast detection path
 
 
-def sp_detect_fast(scores, radius, pad, threshold, k):
+def sp_detect_fast(scores, radius, pad, threshold, k, image_hw=None):
     """NMS + border removal + top-k through the candidate list (nms_radius 1..4).
+    image_hw: optional int32 device tensor [B,2] = (h, w) of the valid region (per-image bottom / right border).
     Returns (nms_map, keypoints, scores, indices, counts)."""
     _require_cuda(scores)
     b, h, w = scores.shape
@@ -159,8 +160,8 @@ def sp_detect_fast(scores, radius, pad, threshold, k):
     cand = torch.empty(b, CANDIDATE_CAPACITY, dtype=torch.int64, device=dev)
     state = torch.empty(2 * b, dtype=torch.int32, device=dev)
     with _timed("sp_nms_border", 2, 8.0 * b * h * w):
-        _lib.check(_lib.lib().b200_sp_nms_border_list(_ptr(scores), b, h, w, int(radius), int(pad or 0), _ptr(nms),
-                                                      _ptr(cand), _ptr(state), CANDIDATE_CAPACITY, _stream()))
+        _lib.check(_lib.lib().b200_sp_nms_border_list(_ptr(scores), b, h, w, int(radius), int(pad or 0), _ptr(image_hw),
+                                                      _ptr(nms), _ptr(cand), _ptr(state), CANDIDATE_CAPACITY, _stream()))
     kpts = torch.empty(b, k, 2, dtype=torch.float32, device=dev)
     ksc = torch.empty(b, k, dtype=torch.float32, device=dev)
     idx = torch.empty(b, k, dtype=torch.int32, device=dev)
@@ -194,14 +195,15 @@ def sp_select_topk(nms_map, threshold, k):
     return kpts, scores, idx, counts
 
 
-def sp_sample_descriptors(dense_nhwc, keypoints, stride=8):
+def sp_sample_descriptors(dense_nhwc, keypoints, stride=8, mode=0):
+    """mode 0: SuperPoint-open grid, 1: nonfree fix_sampling, 2: nonfree legacy (align_corners=True)."""
     _require_cuda(dense_nhwc, keypoints)
     b, hc, wc, c = dense_nhwc.shape
     k = keypoints.shape[1]
     out = torch.empty(b, k, c, dtype=torch.float32, device=dense_nhwc.device)
     with _timed("sp_sample_desc", 1, b * k * c * 4 * 5.0):
-        _lib.check(_lib.lib().b200_sp_sample_descriptors(_ptr(dense_nhwc), b, hc, wc, c, _ptr(keypoints), k, int(stride),
-                                                         _ptr(out), _stream()))
+        _lib.check(_lib.lib().b200_sp_sample_descriptors_mode(_ptr(dense_nhwc), b, hc, wc, c, _ptr(keypoints), k,
+                                                              int(stride), int(mode), _ptr(out), _stream()))
     return out
 
 
@@ -261,3 +263,37 @@ def lg_scatter_matches(m0, m1, ms0, ms1, ind, n0, n1, out_m0, out_m1, out_ms0, o
     with _timed("lg_scatter_matches", 1, (n0 + n1) * 40.0):
         _lib.check(_lib.lib().b200_lg_scatter_matches(_ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ind), int(n0), int(n1),
                                                       _ptr(out_m0), _ptr(out_m1), _ptr(out_ms0), _ptr(out_ms1), _stream()))
+
+
+# ---- SuperGlue configuration ----------------------------------------------------------------------
+def sg_kenc_head(kpts, scores, size, w1, b1, w2, b2, out, row0=0):
+    """normalize_keypoints + first two keypoint-encoder layers -> bf16 rows [row0, row0 + B*n) of out [T,64]."""
+    _require_cuda(kpts, scores, size, out)
+    b, n, _ = kpts.shape
+    with _timed("sg_kenc_head", 1, b * n * 140.0):
+        _lib.check(_lib.lib().b200_sg_keypoint_encoder_head(_ptr(kpts), _ptr(scores), _ptr(size), b, n, _ptr(w1), _ptr(b1),
+                                                            _ptr(w2), _ptr(b2), _ptr(out, row0 * 64), _stream()))
+
+
+def sg_split_hilo(x32, rows, split_row, out):
+    with _timed("sg_split_hilo", 1, rows * 256 * 10.0):
+        _lib.check(_lib.lib().b200_sg_split_hilo(_ptr(x32), int(rows), int(split_row), _ptr(out), _stream()))
+
+
+def sg_sinkhorn_assignment(cost, bin_score, iters, threshold):
+    """log_optimal_transport + mutual-NN filter: (scores [B,M+1,N+1], m0, m1, ms0, ms1)."""
+    _require_cuda(cost, bin_score)
+    b, m, n = cost.shape
+    dev = cost.device
+    ws = torch.empty(_lib.lib().b200_sg_sinkhorn_workspace(b, m, n), dtype=torch.uint8, device=dev)
+    scores = torch.empty(b, m + 1, n + 1, dtype=torch.float32, device=dev)
+    m0 = torch.empty(b, m, dtype=torch.int64, device=dev)
+    m1 = torch.empty(b, n, dtype=torch.int64, device=dev)
+    ms0 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    ms1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    # algorithmic bytes: one pass over the couplings per iteration (+ the final write)
+    with _timed("sg_sinkhorn", 4, 4.0 * b * (m + 1) * (n + 1) * (iters + 2)):
+        _lib.check(_lib.lib().b200_sg_sinkhorn_assignment(_ptr(cost), _ptr(bin_score), b, m, n, int(iters), float(threshold),
+                                                          _ptr(ws), _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0),
+                                                          _ptr(ms1), _stream()))
+    return scores, m0, m1, ms0, ms1

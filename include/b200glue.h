@@ -164,6 +164,9 @@ int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, 
 int b200_sg_keypoint_encoder_head(const float* keypoints, const float* scores, const float* image_size, int B, int n,
                                   const float* w1 /*[32,3]*/, const float* b1, const float* w2 /*[64,32]*/,
                                   const float* b2, void* out, b200_stream_t stream);
+/* fp32 [rows,256] -> bf16 [rows,768] two-term split feeding a K = 768 similarity GEMM with near-fp32 accuracy:
+ * rows < split_row: [hi|hi|lo] (A side), the others: [hi|lo|hi] (B side).  Used for the score einsum (:284-285). */
+int b200_sg_split_hilo(const float* x, long long rows, long long split_row, void* out, b200_stream_t stream);
 /* log_optimal_transport (:173-201) on cost [B,M,N] with the dustbin score *bin_score (device scalar),
  * `iters` Sinkhorn iterations in one persistent cooperative kernel, then the mutual-NN filter (:288-298).
  * scores [B,M+1,N+1]; matches int64, -1 = unmatched.  Precondition: |cost| < ~60 (fp32 exp range). */
