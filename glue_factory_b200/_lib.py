@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200glue.so")
+# B200GLUE_LIB points at an alternative build of the same library (kernel experiments); never a fallback
+LIB_PATH = os.environ.get("B200GLUE_LIB") or os.path.join(_HERE, "libb200glue.so")
 
 EPI_BIAS_BF16, EPI_QKV_ROTARY, EPI_LN_GELU, EPI_RESID, EPI_F32 = 0, 1, 2, 3, 4
 EPI_CONV_RELU_BN, EPI_CONV_BN_L2, EPI_CONV_BN_SOFTMAX_D2S = 5, 6, 7

@@ -3,12 +3,16 @@
 // One CTA per (pair of 128-query tiles, head, sequence); 1 CTA per SM (TMEM: S0 S1 O0 O1 = 384 columns).
 //   warp 0      TMA producer: Q tiles once, K/V tiles through a ring of kKvStages smem slots
 //   warp 1      TMEM allocation + single-thread tcgen05.mma issue
-//   warps 2-5   softmax group 0 (query tile 0), one query row per thread
-//   warps 6-9   softmax group 1 (query tile 1)
+//   warps 2-9   softmax group 0 (query tile 0): two threads per query row, 64 keys of the tile each
+//   warps 10-17 softmax group 1 (query tile 1)
 // Per 128-key tile and group g:
 //   S_g = Q_g K^T    (tcgen05.mma M=128 N=128 K=64, fp32 in TMEM)
-//   the group's 128 threads pull their S row into registers (tcgen05.ld) and release S_g at once, so the
-//   next S_g is computed while this one is exponentiated; P_g -> smem as bf16 (128B-swizzled, K-major)
+//   the group's 256 threads pull their half S row into registers (tcgen05.ld) and release S_g at once, so
+//   the next S_g is computed while this one is exponentiated; P_g -> smem as bf16 (128B-swizzled, K-major).
+//   The two threads of a row (same TMEM lane quarter, warps w and w+4) agree on the row maximum through
+//   smem and a 64-thread named barrier, keep partial row sums, and each rescales / writes half of O.
+//   Four softmax warps per scheduler (instead of two whole-row warps) hide the FFMA -> MUFU -> FADD
+//   latencies that the two-warp version left exposed.
 //   O_g += P_g V     (tcgen05.mma M=128 N=64 K=128, accumulating in TMEM; V consumed token-major through
 //                     an MN-major descriptor)
 // Online softmax with a lazily updated reference maximum: the running maximum m only moves (and O_g /
@@ -28,15 +32,27 @@
 
 namespace b200 {
 
-constexpr int kAttThreads = 320;
+constexpr int kAttThreads = 576;
+constexpr int kSoftmaxWarpsPerGroup = 8;
 constexpr int kQTile = 128, kKvTile = 128, kHeadDim = 64;
 constexpr int kQPerCta = 2 * kQTile;
 constexpr int kTileBytes = 128 * 64 * 2;  // 16 KB: 128 rows x 64 bf16
-constexpr int kKvStages = 3;
-// smem: Q[2] | K[stages] | V[stages] | P[2 groups][2 halves of 64 keys] | barriers
-constexpr int kAttSmemBytes = kTileBytes * (2 + 2 * kKvStages + 4) + 1024 + 256;
-constexpr uint32_t kAttTmemCols = 512;  // S0: [0,128)  S1: [128,256)  O0: [256,320)  O1: [320,384)
+constexpr int kKvStages = 4;
+// smem: Q[2] | K[stages] | V[stages] | barriers | row exchange
+constexpr int kAttXchBytes = 3 * 2 * 2 * 128 * 4;  // [2 parities + row sums][group][half][row] floats
+constexpr int kAttSmemBytes = kTileBytes * (2 + 2 * kKvStages) + 1024 + 256 + kAttXchBytes;
+// S0: [0,128)  S1: [128,256)  O0: [256,320)  O1: [320,384)  P0: [384,448)  P1: [448,512) (bf16 pairs)
+constexpr uint32_t kAttTmemCols = 512;
 
+#ifndef ATT_X
+#define ATT_X 0
+#endif
+#if ATT_X & 512
+__device__ long long g_att_trace[2][16][8];
+#define ATT_T(role, j, slot) do { if (blockIdx.x == 1 && blockIdx.y == 1 && blockIdx.z == 3 && (j) >= 4 && (j) < 12) g_att_trace[role][j][slot] = clock64(); } while (0)
+#else
+#define ATT_T(role, j, slot) do {} while (0)
+#endif
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -51,8 +67,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     uint8_t* sQ = smem;
     uint8_t* sK = sQ + 2 * kTileBytes;
     uint8_t* sV = sK + kKvStages * kTileBytes;
-    uint8_t* sP = sV + kKvStages * kTileBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 4 * kTileBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kKvStages * kTileBytes);
     uint64_t* q_full = bars;                     // [2]
     uint64_t* k_full = q_full + 2;               // [kKvStages]
     uint64_t* v_full = k_full + kKvStages;       // [kKvStages]
@@ -62,12 +77,16 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     uint64_t* p_ready = s_free + 2;              // [2]
     uint64_t* o_full = p_ready + 2;              // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+    float* xch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warp index / TMEM base / lengths go through a shuffle so that the compiler treats them, and the UMMA
+    // operands derived from them, as warp-uniform: tcgen05.mma then issues straight from uniform registers
+    // (a per-lane operand costs an ELECT / R2UR loop of ~75 clk around every MMA)
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int seq = blockIdx.z, head = blockIdx.y, qt = blockIdx.x;
     const AttnSeq sd = p.seqs[seq];
-    const int q_len = p.len_override ? p.len_override[sd.q_len_slot] : sd.q_len;
-    const int kv_len = p.len_override ? p.len_override[sd.kv_len_slot] : sd.kv_len;
+    const int q_len = __shfl_sync(0xffffffffu, p.len_override ? p.len_override[sd.q_len_slot] : sd.q_len, 0);
+    const int kv_len = __shfl_sync(0xffffffffu, p.len_override ? p.len_override[sd.kv_len_slot] : sd.kv_len, 0);
     if (qt * kQPerCta >= q_len) return;  // uniform for the whole CTA, before any barrier / TMEM use
     const int kv_tiles = (kv_len + kKvTile - 1) / kKvTile;
     const bool g1_active = qt * kQPerCta + kQTile < q_len;  // second query tile holds at least one row
@@ -79,8 +98,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         for (int g = 0; g < 2; ++g) {
             mbar_init(q_full + g, 1);
             mbar_init(s_full + g, 1);
-            mbar_init(s_free + g, 4);
-            mbar_init(p_ready + g, 4);
+            mbar_init(s_free + g, kSoftmaxWarpsPerGroup);
+            mbar_init(p_ready + g, kSoftmaxWarpsPerGroup);
             mbar_init(o_full + g, 1);
         }
         for (int s = 0; s < kKvStages; ++s) {
@@ -94,7 +113,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -121,17 +140,22 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0 && kv_tiles > 0) {
+        // the whole warp walks the loop (uniform control flow, uniform operands); one lane issues
+        if (kv_tiles > 0) {
+            const bool leader = elect_one();
             constexpr uint32_t idesc_s = umma_idesc(128, 128, 1u, 0u, 0u);  // Q, K both K-major
-            constexpr uint32_t idesc_o = umma_idesc(128, 64, 1u, 0u, 1u);   // P K-major, V MN-major
+            constexpr uint32_t idesc_o = umma_idesc(128, 64, 1u, 0u, 1u);   // P K-major (TMEM), V MN-major
             const int groups = g1_active ? 2 : 1;
             auto issue_s = [&](int g, int stage) {
                 const uint32_t aq = smem_u32(sQ + g * kTileBytes), bk = smem_u32(sK + stage * kTileBytes);
+                if (leader) {
 #pragma unroll
-                for (int k = 0; k < kHeadDim / 16; ++k)
-                    umma_f16(tmem_base + g * 128, umma_smem_desc_sw128(aq + k * 32, 1024, 16),
-                             umma_smem_desc_sw128(bk + k * 32, 1024, 16), idesc_s, k != 0 ? 1u : 0u);
-                umma_commit(s_full + g);
+                    for (int k = 0; k < kHeadDim / 16; ++k)
+                        umma_f16(tmem_base + g * 128, umma_smem_desc_sw128(aq + k * 32, 1024, 16),
+                                 umma_smem_desc_sw128(bk + k * 32, 1024, 16), idesc_s, k != 0 ? 1u : 0u);
+                    umma_commit(s_full + g);
+                }
+                __syncwarp();
             };
             mbar_wait(k_full, 0);
             for (int g = 0; g < groups; ++g) {
@@ -149,63 +173,84 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     for (int g = 0; g < groups; ++g) {
                         mbar_wait(s_free + g, j & 1);  // the group holds S_g(j) in registers
                         tc_fence_after();
+                        if (leader) ATT_T(0, j, g * 2);
                         issue_s(g, next_stage);
+                        if (leader) ATT_T(0, j, g * 2 + 1);
                     }
                 }
                 mbar_wait(v_full + stage, phase);
                 for (int g = 0; g < groups; ++g) {
-                    mbar_wait(p_ready + g, j & 1);  // P_g(j) is in smem (and O_g rescaled if it had to be)
+                    mbar_wait(p_ready + g, j & 1);  // P_g(j) is in TMEM (and O_g rescaled if it had to be)
                     tc_fence_after();
-                    const uint32_t ap = smem_u32(sP + g * 2 * kTileBytes), bv = smem_u32(sV + stage * kTileBytes);
+                    const uint32_t bv = smem_u32(sV + stage * kTileBytes);
+                    if (leader) ATT_T(0, j, 4 + g * 2);
+                    if (leader) {
 #pragma unroll
-                    for (int k = 0; k < kKvTile / 16; ++k)
-                        umma_f16(tmem_base + 256 + g * 64,
-                                 umma_smem_desc_sw128(ap + (k >> 2) * kTileBytes + (k & 3) * 32, 1024, 16),
-                                 umma_smem_desc_sw128(bv + k * 2048, 1024, 1024), idesc_o, (j | k) != 0 ? 1u : 0u);
-                    umma_commit(o_full + g);
+                        for (int k = 0; k < kKvTile / 16; ++k)
+                            umma_f16_ts(tmem_base + 256 + g * 64, tmem_base + 384 + g * 64 + k * 8,
+                                        umma_smem_desc_sw128(bv + k * 2048, 1024, 1024), idesc_o,
+                                        (j | k) != 0 ? 1u : 0u);
+                        umma_commit(o_full + g);
+                    }
+                    __syncwarp();
+                    if (leader) ATT_T(0, j, 5 + g * 2);
                 }
-                umma_commit(kv_empty + stage);  // K_j / V_j are free once everything issued so far retires
+                if (leader) umma_commit(kv_empty + stage);  // K_j / V_j are free once everything issued so far retires
+                __syncwarp();
                 stage = next_stage;
                 phase = next_phase;
             }
         }
     } else {
-        // ===================== softmax + output warps: thread <-> query row =====================
-        const int g = (warp - 2) >> 2;
-        const int quarter = warp & 3;
+        // ============ softmax + output warps: two threads per query row, 64 keys / 32 output dims each ============
+        const int sw = warp - 2;
+        const int g = sw >> 3;
+        const int half = (sw >> 2) & 1;
+        const int quarter = warp & 3;  // TMEM lane quarter this warp may touch
         const int row = quarter * 32 + lane;  // row inside the query tile == TMEM lane
         const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
-        const uint32_t tmem_s = tmem_base + g * 128 + lane_off, tmem_o = tmem_base + 256 + g * 64 + lane_off;
-        uint8_t* myP = sP + g * 2 * kTileBytes + row * 128;
+        const uint32_t tmem_s = tmem_base + g * 128 + half * 64 + lane_off;
+        const uint32_t tmem_o = tmem_base + 256 + g * 64 + half * 32 + lane_off;
+        const uint32_t tmem_p = tmem_base + 384 + g * 64 + half * 32 + lane_off;
         const int q_idx = qt * kQPerCta + g * kQTile + row;
+        const int pair_bar = 1 + g * 4 + quarter;  // named barrier shared by the row's two warps
+        float* x_mine = xch + (g * 2 + half) * 128 + row;
+        float* x_other = xch + (g * 2 + (half ^ 1)) * 128 + row;
         if (g == 0 || g1_active) {
             const float c = p.scale * 1.4426950408889634f;  // softmax(scale * s) via exp2
             float m_run = -INFINITY, l_run = 0.f;
-            float sv[kKvTile];
+            float sv[64];
             uint32_t r[32];
             for (int j = 0; j < kv_tiles; ++j) {
-                const int valid = min(kKvTile, kv_len - j * kKvTile);
+                const int valid = min(kKvTile, kv_len - j * kKvTile) - half * 64;
                 mbar_wait(s_full + g, j & 1);
                 tc_fence_after();
-#pragma unroll
-                for (int ch = 0; ch < 4; ++ch) B200_TMEM_LD32F(tmem_s + ch * 32, sv + ch * 32);
+                if (sw == 0 && lane == 0) ATT_T(1, j, 0);
+                B200_TMEM_LD32F(tmem_s, sv);
+                B200_TMEM_LD32F(tmem_s + 32, sv + 32);
                 tmem_ld_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(s_free + g);  // S_g(j+1) may overwrite the TMEM buffer now
-                if (valid < kKvTile) {
+                if (sw == 0 && lane == 0) ATT_T(1, j, 1);
+                if (valid < 64) {
 #pragma unroll
-                    for (int i = 0; i < kKvTile; ++i)
+                    for (int i = 0; i < 64; ++i)
                         if (i >= valid) sv[i] = -INFINITY;
                 }
                 float m0 = sv[0], m1 = sv[1], m2 = sv[2], m3 = sv[3];
 #pragma unroll
-                for (int i = 4; i < kKvTile; i += 4) {
+                for (int i = 4; i < 64; i += 4) {
                     m0 = fmaxf(m0, sv[i]); m1 = fmaxf(m1, sv[i + 1]);
                     m2 = fmaxf(m2, sv[i + 2]); m3 = fmaxf(m3, sv[i + 3]);
                 }
-                const float m_tile = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                const int par = (j & 1) * 512;
+                x_mine[par] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+                asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+                const float m_tile = fmaxf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)), x_other[par]);
                 // lazy rescale: move the reference maximum only when it is off by more than 2^8
+                // (both threads of a row see the same m_tile / m_run, hence take the same decision)
+                if (sw == 0 && lane == 0) ATT_T(1, j, 2);
                 const bool need = (m_tile - m_run) * c > 8.0f;  // always true for j == 0 (m_run = -inf)
                 bool waited = false;
                 if (j > 0 && __any_sync(0xffffffffu, need)) {
@@ -217,7 +262,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     l_run *= alpha;
                     m_run = m_new;
 #pragma unroll 1
-                    for (int ch = 0; ch < 8; ++ch) {  // 8 columns at a time: S_g sits in registers meanwhile
+                    for (int ch = 0; ch < 4; ++ch) {  // this thread's 32 of the 64 O columns, 8 at a time
                         uint32_t t8[8];
                         tmem_ld8(tmem_o + ch * 8, t8);
                         tmem_ld_wait();
@@ -233,53 +278,52 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     mbar_wait(o_full + g, (j - 1) & 1);  // PV_g(j-1) has finished reading the P buffer
                     tc_fence_after();
                 }
+                if (sw == 0 && lane == 0) ATT_T(1, j, 3);
                 const float mc = m_run * c;
                 float l0 = 0.f, l1 = 0.f;
 #pragma unroll
-                for (int ch = 0; ch < 16; ++ch) {  // 16 chunks of 8 keys = 16 bytes each
-                    uint32_t pk[4];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float e0 = ex2_approx(fmaf(sv[ch * 8 + 2 * i], c, -mc));
-                        const float e1 = ex2_approx(fmaf(sv[ch * 8 + 2 * i + 1], c, -mc));
-                        l0 += e0;
-                        l1 += e1;
-                        pk[i] = pack_bf16(e0, e1);
-                    }
-                    uint8_t* base = myP + (ch >> 3) * kTileBytes;
-                    *reinterpret_cast<uint4*>(base + (((ch & 7) ^ (row & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                for (int i = 0; i < 32; ++i) {  // column i of the P row = keys (2i, 2i+1) as bf16
+                    const float e0 = ex2_approx(fmaf(sv[2 * i], c, -mc));
+                    const float e1 = ex2_approx(fmaf(sv[2 * i + 1], c, -mc));
+                    l0 += e0;
+                    l1 += e1;
+                    r[i] = pack_bf16(e0, e1);
                 }
+                tmem_st32(tmem_p, r);
+                tmem_st_wait();
                 l_run += l0 + l1;
+                if (sw == 0 && lane == 0) ATT_T(1, j, 4);
                 tc_fence_before();
-                fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(p_ready + g);
+                if (sw == 0 && lane == 0) ATT_T(1, j, 5);
             }
+            // total row sum = the two partial sums (taken against the same reference maximum)
+            x_mine[1024] = l_run;
+            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+            l_run += x_other[1024];
             if (kv_tiles > 0) {
                 mbar_wait(o_full + g, (kv_tiles - 1) & 1);
                 tc_fence_after();
             }
             const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;  // no keys: zeros
             __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)(sd.q_row0 + q_idx) * p.ld_out +
-                                 p.out_col0 + head * kHeadDim;
+                                 p.out_col0 + head * kHeadDim + half * 32;
+            if (kv_tiles > 0) {
+                tmem_ld32(tmem_o, r);
+                tmem_ld_wait();
+            } else {
 #pragma unroll
-            for (int ch = 0; ch < 2; ++ch) {
-                if (kv_tiles > 0) {
-                    tmem_ld32(tmem_o + ch * 32, r);
-                    tmem_ld_wait();
-                } else {
+                for (int i = 0; i < 32; ++i) r[i] = 0u;
+            }
+            if (q_idx < q_len) {
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) r[i] = 0u;
-                }
-                if (q_idx < q_len) {
-#pragma unroll
-                    for (int i = 0; i < 32; i += 8)
-                        *reinterpret_cast<uint4*>(dst + ch * 32 + i) = make_uint4(
-                            pack_bf16(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv),
-                            pack_bf16(__uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv),
-                            pack_bf16(__uint_as_float(r[i + 4]) * inv, __uint_as_float(r[i + 5]) * inv),
-                            pack_bf16(__uint_as_float(r[i + 6]) * inv, __uint_as_float(r[i + 7]) * inv));
-                }
+                for (int i = 0; i < 32; i += 8)
+                    *reinterpret_cast<uint4*>(dst + i) = make_uint4(
+                        pack_bf16(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv),
+                        pack_bf16(__uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv),
+                        pack_bf16(__uint_as_float(r[i + 4]) * inv, __uint_as_float(r[i + 5]) * inv),
+                        pack_bf16(__uint_as_float(r[i + 6]) * inv, __uint_as_float(r[i + 7]) * inv));
             }
         }
     }
@@ -287,6 +331,12 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     __syncthreads();
     if (warp == 1) tmem_dealloc<kAttTmemCols>(tmem_base);
 }
+
+#if ATT_X & 512
+extern "C" int b200_debug_attention_trace(long long* dst) {
+    return (int)cudaMemcpyFromSymbol(dst, g_att_trace, sizeof(g_att_trace));
+}
+#endif
 
 int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                      int num_seqs, int max_q_len, int heads, cudaStream_t stream) {

@@ -65,7 +65,9 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint8_t* sStage = sA + Cfg::kStages * kCpPatchBytes + 256;              // [128 px][COUT] bf16, swizzled
     float* sPar = reinterpret_cast<float*>(sStage + 128 * COUT * 2);        // bias | scale | shift
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warp index / TMEM base through a shuffle: the compiler then treats them (and every UMMA operand derived
+    // from them) as warp-uniform and issues tcgen05.mma straight from uniform registers
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const long long total_tiles = (long long)p.batch * tiles_per_img;
 
@@ -87,7 +89,7 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     if (warp == 0) {
         if (lane == 0) {
@@ -107,18 +109,19 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc(128, COUT, 1u, 0u, 0u);
-            mbar_wait(w_full, 0);
-            int stage = 0, acc = 0;
-            uint32_t phase = 0, acc_phase = 0;
-            const uint32_t w0 = smem_u32(sW);
-            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-                mbar_wait(acc_empty + acc, acc_phase ^ 1);
-                mbar_wait(full_bar + stage, phase);
-                tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * COUT;
-                const uint32_t a0 = smem_u32(sA + stage * kCpPatchBytes);
+        // whole warp walks the tile loop (uniform control flow); one elected lane issues the MMAs / commits
+        constexpr uint32_t idesc = umma_idesc(128, COUT, 1u, 0u, 0u);
+        mbar_wait(w_full, 0);
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        const uint32_t w0 = smem_u32(sW);
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            mbar_wait(acc_empty + acc, acc_phase ^ 1);
+            mbar_wait(full_bar + stage, phase);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + acc * COUT;
+            const uint32_t a0 = smem_u32(sA + stage * kCpPatchBytes);
+            if (elect_one()) {
 #pragma unroll
                 for (int tap = 0; tap < 9; ++tap) {
                     const int dy = tap / 3, dx = tap - dy * 3;
@@ -131,9 +134,10 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 }
                 umma_commit(empty_bar + stage);
                 umma_commit(acc_full + acc);
-                if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
-                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
+            __syncwarp();
+            if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     } else {
         // ===================== epilogue (128 threads) =====================

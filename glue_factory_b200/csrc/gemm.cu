@@ -374,7 +374,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_par + kParamFloats);
     float2* s_exch = reinterpret_cast<float2*>(s_stage + kEpiWarps * kStageBytesPerWarp);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warp index / TMEM base through a shuffle: the compiler then keeps every UMMA operand in uniform registers
+    // (per-lane operands cost an ELECT / R2UR loop of ~75 clk around each tcgen05.mma)
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
 
     const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
     const int n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
@@ -398,7 +400,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -435,21 +437,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc(kBlockM, Cfg::kUmmaN, 1u, 0u, 0u);
-            int stage = 0;
-            uint32_t phase = 0;
-            int acc = 0;
-            uint32_t acc_phase = 0;
-            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-                mbar_wait(acc_empty + acc, acc_phase ^ 1);
+        // the whole warp walks the loop (uniform control flow); one elected lane issues MMAs and commits
+        const bool leader = elect_one();
+        constexpr uint32_t idesc = umma_idesc(kBlockM, Cfg::kUmmaN, 1u, 0u, 0u);
+        int stage = 0;
+        uint32_t phase = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            mbar_wait(acc_empty + acc, acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                mbar_wait(full_bar + stage, phase);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
-                for (int kb = 0; kb < k_blocks; ++kb) {
-                    mbar_wait(full_bar + stage, phase);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-                    const uint32_t sb = sa + Cfg::kABytes;
+                const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+                const uint32_t sb = sa + Cfg::kABytes;
+                if (leader) {
 #pragma unroll
                     for (int k = 0; k < kBlockK / 16; ++k) {
                         const uint64_t adesc = umma_smem_desc_sw128(sa + k * 32, 1024, 16);
@@ -461,11 +465,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                         }
                     }
                     umma_commit(empty_bar + stage);  // frees the smem slot once these MMAs retire
-                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(acc_full + acc);
-                if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+                __syncwarp();
+                if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
             }
+            if (leader) umma_commit(acc_full + acc);
+            __syncwarp();
+            if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
         }
     } else {
         // ===================== epilogue warps (TMEM lanes 32*(warp%4) ..) =====================
