@@ -234,8 +234,8 @@ int b200_attention(const b200_attn_desc* d, b200_stream_t stream_) {
                  "attention: output must be 16-byte aligned");
     CUtensorMap tq, tk, tv;
     if (make_map_2d(&tq, d->q, d->q_rows, d->ldq, d->ldq, 128) != 0) return -1;
-    if (make_map_2d(&tk, d->k, d->k_rows, d->ldk, d->ldk, 128) != 0) return -1;
-    if (make_map_2d(&tv, d->v, d->v_rows, d->ldv, d->ldv, 128) != 0) return -1;
+    if (make_map_2d(&tk, d->k, d->k_rows, d->ldk, d->ldk, 64) != 0) return -1;  // 64-key tiles
+    if (make_map_2d(&tv, d->v, d->v_rows, d->ldv, d->ldv, 64) != 0) return -1;
     AttnParams p;
     p.seqs = reinterpret_cast<const AttnSeq*>(d->seqs);
     p.len_override = d->len_override;

@@ -404,19 +404,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-                const int nt = (int)(t % n_tiles);
-                const long long rest = t / n_tiles;
-                const int mt = (int)(rest % m_tiles);
-                const int b = (int)(rest / m_tiles);
-                const int brow = b * p.b_batch_rows + nt * BLOCK_N;
-                for (int kb = 0; kb < k_blocks; ++kb) {
-                    mbar_wait(empty_bar + stage, phase ^ 1);
-                    uint8_t* sa = smem + stage * Cfg::kStageBytes;
-                    uint8_t* sb = sa + Cfg::kABytes;
+        // whole warp walks the loop (uniform coordinates in uniform registers); one elected lane issues
+        const bool leader = elect_one();
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            const int nt = (int)(t % n_tiles);
+            const long long rest = t / n_tiles;
+            const int mt = (int)(rest % m_tiles);
+            const int b = (int)(rest / m_tiles);
+            const int brow = b * p.b_batch_rows + nt * BLOCK_N;
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                mbar_wait(empty_bar + stage, phase ^ 1);
+                uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                uint8_t* sb = sa + Cfg::kABytes;
+                if (leader) {
                     mbar_arrive_expect_tx(full_bar + stage, Cfg::kStageBytes);
                     if constexpr (A_MODE == 0) {
                         tma_load_2d(sa, &tmap_a, full_bar + stage, kb * kBlockK, b * p.a_batch_rows + mt * kBlockM);
@@ -431,8 +433,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     for (int h = 0; h < Cfg::kNumUmmaN; ++h)
                         tma_load_2d(sb + h * Cfg::kUmmaN * kBlockK * 2, &tmap_b, full_bar + stage, kb * kBlockK,
                                     brow + h * Cfg::kUmmaN);
-                    if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {

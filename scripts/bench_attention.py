@@ -51,10 +51,9 @@ if hasattr(h, "b200_debug_attention_trace"):
 
     buf = np.zeros((2, 16, 8), dtype=np.int64)
     h.b200_debug_attention_trace(ctypes.c_void_p(buf.ctypes.data))
-    t0 = buf[0, 4, 0]
-    print("MMA thread: [wait s_free0, S0 issued, wait s_free1, S1 issued, wait p_ready0, PV0 issued, wait p_ready1, PV1 issued]")
-    for j in range(4, 12):
-        print(j, (buf[0, j] - t0).tolist())
-    print("softmax g0: [s_full seen, S in regs + s_free, max + pair sync, o_full seen, exps done, p_ready arrived]")
-    for j in range(4, 12):
-        print(j, (buf[1, j, :6] - t0).tolist())
+    t0 = buf[0, 0, 0]
+    print("issuer, key tiles 8..23: [S g0, -, S g1, -, PV g0, -, PV g1, -]; softmax g0 warp 0: [S seen, in regs, max, exps, P stored]")
+    for j in range(16):
+        a = (buf[0, j] - t0)[[0, 2, 4, 6]].tolist()
+        b = (buf[1, j, :5] - t0).tolist()
+        print(j + 8, a, b)
