@@ -8,6 +8,7 @@
 
 #include "../../include/b200glue.h"
 #include "attention.cuh"
+#include "conv_stem.cuh"
 #include "common.cuh"
 #include "gemm.cuh"
 #include "lg_kernels.cuh"
@@ -28,6 +29,7 @@ int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const C
                 const GemmParams& p, int num_sms, cudaStream_t stream);
 int launch_conv_patch(int cout, const CUtensorMap& ta, const CUtensorMap& tw, const GemmParams& p, int num_sms,
                       cudaStream_t stream);
+int launch_conv_stem(const CUtensorMap& tw, const StemParams& p, int num_sms, cudaStream_t stream);
 int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
                      int num_seqs, int max_q_len, int heads, cudaStream_t stream);
 
@@ -248,6 +250,32 @@ int b200_attention(const b200_attn_desc* d, b200_stream_t stream_) {
 int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* w, const float* bias,
                    const float* scale, const float* shift, void* out_nhwc, b200_stream_t stream) {
     return launch_conv1a(image, B, C, H, W, w, bias, scale, shift, out_nhwc, static_cast<cudaStream_t>(stream));
+}
+int b200_sp_conv_stem(const float* image, int B, int C, int H, int W, const float* w1, const float* host_params,
+                      const void* w2, int pool, void* out_nhwc, b200_stream_t stream) {
+    B200_REQUIRE(image && w1 && host_params && w2 && out_nhwc, "conv_stem: null argument");
+    B200_REQUIRE(C == 1 || C == 3, "conv_stem: image must have 1 or 3 channels, got %d", C);
+    B200_REQUIRE(B >= 0 && H > 0 && W > 0, "conv_stem: bad sizes");
+    B200_REQUIRE(!pool || (H % 2 == 0 && W % 2 == 0), "conv_stem: pooling needs even H and W");
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(out_nhwc) & 15) == 0 && (reinterpret_cast<uintptr_t>(w2) & 15) == 0,
+                 "conv_stem: output and weights must be 16-byte aligned");
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, host_params) == cudaSuccess)
+        B200_REQUIRE(attr.type != cudaMemoryTypeDevice, "conv_stem: the per-channel operands must be in HOST memory");
+    else
+        cudaGetLastError();
+    const int num_sms = sm_count();
+    B200_REQUIRE(num_sms > 0, "conv_stem: no CUDA device available");
+    CUtensorMap tw;
+    if (make_map_2d(&tw, w2, 64, 576, 576, 64) != 0) return -1;
+    StemParams p;
+    p.img = image; p.B = B; p.C = C; p.H = H; p.W = W;
+    p.w1 = w1;
+    memcpy(p.par, host_params, sizeof(p.par));
+    p.pool = pool;
+    p.out = reinterpret_cast<__nv_bfloat16*>(out_nhwc);
+    p.tiles_x = (W + 7) / 8; p.tiles_y = (H + 15) / 16;
+    return launch_conv_stem(tw, p, num_sms, static_cast<cudaStream_t>(stream));
 }
 int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders, float* out,
                        b200_stream_t stream) {

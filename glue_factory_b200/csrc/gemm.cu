@@ -23,11 +23,18 @@ namespace b200 {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int kTileH = 8, kTileW = 16;  // conv M-tile: 8 x 16 pixels
-constexpr int kEpiWarps = 8;            // two warps per TMEM lane quarter, interleaved 32-column chunks
-constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
+// epilogue warps: two per TMEM lane quarter (interleaved 32-column chunks); four per quarter for the
+// LayerNorm + GELU epilogue, which is latency-bound per warp and cannot overlap the MMA (its 128 x 512 fp32
+// accumulator fills the TMEM), so it needs the extra warps to keep the schedulers busy
+constexpr int kEpiWarps = 8;
+constexpr int kEpiWarpsLn = 16;
+__host__ __device__ constexpr int epi_warps(int epi) { return epi == EPI_LN_GELU ? kEpiWarpsLn : kEpiWarps; }
+__host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged in smem (bias | scale/gamma | shift/beta)
 constexpr int kStageBytesPerWarp = 4096;  // 32 rows x 128 B staging per epilogue warp
-constexpr int kEpiSmemBytes = kParamFloats * 4 + kEpiWarps * kStageBytesPerWarp + 128 * 2 * 8;
+constexpr int kStageBytesPerWarpLn = 2048;  // 32 rows x 64 B in the LayerNorm + GELU epilogue
+static_assert(kEpiWarps * kStageBytesPerWarp == kEpiWarpsLn * kStageBytesPerWarpLn, "one staging area for both layouts");
+constexpr int kEpiSmemBytes = kParamFloats * 4 + kEpiWarps * kStageBytesPerWarp + 128 * 4 * 8;
 
 template <int BLOCK_N>
 struct GemmCfg {
@@ -68,7 +75,8 @@ __device__ __forceinline__ void store16B(void* p, uint32_t a, uint32_t b, uint32
     *reinterpret_cast<uint4*>(p) = make_uint4(a, b, c, d);
 }
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
+template <int WARPS>
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * WARPS) : "memory"); }
 
 // epilogue-side view of shared memory
 struct EpiSmem {
@@ -180,7 +188,7 @@ __device__ __forceinline__ void epilogue_ln_gelu(const GemmParams& p, const EpiS
     uint32_t r[32];
     float sum = 0.f, sumsq = 0.f;
 #pragma unroll 1
-    for (int c = half; c < 16; c += 2) {
+    for (int c = half; c < 16; c += 4) {
         tmem_ld32(acc_taddr + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
@@ -194,16 +202,19 @@ __device__ __forceinline__ void epilogue_ln_gelu(const GemmParams& p, const EpiS
     }
     const int row = quarter * 32 + lane;
     es.exch[half * 128 + row] = make_float2(sum, sumsq);
-    epi_bar_sync();
-    const float2 other = es.exch[(half ^ 1) * 128 + row];
-    sum += other.x;
-    sumsq += other.y;
+    epi_bar_sync<kEpiWarpsLn>();
+#pragma unroll
+    for (int o = 1; o < 4; ++o) {  // the row's other three column groups
+        const float2 other = es.exch[((half + o) & 3) * 128 + row];
+        sum += other.x;
+        sumsq += other.y;
+    }
     const float mean = sum * (1.0f / 512.f);
     const float var = fmaxf(sumsq * (1.0f / 512.f) - mean * mean, 0.f);
     const float rstd = rsqrtf(var + p.ln_eps);
     const float nmr = -mean * rstd;
 #pragma unroll 1
-    for (int c = half; c < 16; c += 2) {
+    for (int c = half; c < 16; c += 4) {
         tmem_ld32(acc_taddr + c * 32, r);
         tmem_ld_wait();
         uint32_t pk[16];
@@ -237,7 +248,7 @@ __device__ __forceinline__ void epilogue_ln_gelu(const GemmParams& p, const EpiS
         }
         __syncwarp();
     }
-    epi_bar_sync();  // exch is rewritten by the next tile
+    epi_bar_sync<kEpiWarpsLn>();  // exch is rewritten by the next tile
 }
 
 // thread-per-row epilogues of the SuperPoint convolutions / heads (per-column operands from smem)
@@ -373,7 +384,7 @@ __device__ __forceinline__ void epilogue_conv(const GemmParams& p, const EpiSmem
 // kernel
 // ---------------------------------------------------------------------------------------------
 template <int BLOCK_N, int EPI, int A_MODE>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmParams p) {
     using Cfg = GemmCfg<BLOCK_N>;
@@ -406,7 +417,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         for (int s = 0; s < Cfg::kAccStages; ++s) {
             mbar_init(acc_full + s, 1);
-            mbar_init(acc_empty + s, kEpiWarps);  // one arrival per epilogue warp
+            mbar_init(acc_empty + s, epi_warps(EPI));  // one arrival per epilogue warp
         }
         fence_barrier_init();
     }
@@ -499,18 +510,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const float* src1 = EPI == EPI_LN_GELU ? p.ln_gamma : p.scale;
             const float* src2 = EPI == EPI_LN_GELU ? p.ln_beta : p.shift;
             const int n = p.N < 768 ? p.N : 768;
-            for (int i = et; i < n; i += 32 * kEpiWarps) {
+            for (int i = et; i < n; i += 32 * epi_warps(EPI)) {
                 if (p.bias != nullptr) s_par[i] = __ldg(p.bias + i);
                 if (src1 != nullptr) s_par[768 + i] = __ldg(src1 + i);
                 if (src2 != nullptr) s_par[1536 + i] = __ldg(src2 + i);
             }
-            epi_bar_sync();
+            epi_bar_sync<epi_warps(EPI)>();
         }
         EpiSmem es;
         es.bias = s_par;
         es.par1 = s_par + 768;
         es.par2 = s_par + 1536;
-        es.stage = s_stage + (warp - 2) * kStageBytesPerWarp;
+        es.stage = s_stage + (warp - 2) * (EPI == EPI_LN_GELU ? kStageBytesPerWarpLn : kStageBytesPerWarp);
         es.exch = s_exch;
         const int r_in_tile = quarter * 32 + lane;
         int acc = 0;
@@ -571,7 +582,7 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
     const long long total = (long long)p.batch * m_tiles * n_tiles;
     if (total == 0) return 0;
     const int grid = (int)(total < num_sms ? total : num_sms);
-    kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ta, tb, p);
+    kern<<<grid, gemm_threads(EPI), Cfg::kSmemBytes, stream>>>(ta, tb, p);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }

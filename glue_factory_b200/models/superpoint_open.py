@@ -13,6 +13,7 @@ libb200glue.so kernels:
 
 There is no PyTorch fallback: CPU tensors raise.
 """
+import os
 from collections import OrderedDict
 from pathlib import Path
 from types import SimpleNamespace
@@ -48,6 +49,10 @@ def _pack_conv(conv):
     return w.permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(torch.bfloat16).contiguous()
 
 
+# B200GLUE_FUSED_STEM=0 keeps conv1a / conv1b as two kernels (A/B comparison of the same CUDA path)
+FUSED_STEM = os.environ.get("B200GLUE_FUSED_STEM", "1") != "0"
+
+
 def sp_dense_forward(P, image):
     """Shared dense path of both SuperPoint variants on packed weights `P` (see SuperPoint._pack):
     image (B,1|3,H,W) fp32 -> heat map (B,8h,8w) fp32, dense descriptors NHWC (B,h,w,256) fp32."""
@@ -56,10 +61,21 @@ def sp_dense_forward(P, image):
     image = image.float().contiguous()
     B, _, H, W = image.shape
     dev = image.device
-    x = torch.empty(B, H, W, 64, dtype=torch.bfloat16, device=dev)
-    ops.sp_conv1a(image, P["c1a_w"], P["c1a_b"], P["c1a_s"], P["c1a_t"], x)
-    h, w = H, W
-    for L in P["convs"]:
+    L0 = P["convs"][0]
+    if FUSED_STEM and L0["cin"] == 64 and L0["cout"] == 64 and (not L0["pool"] or (H % 2 == 0 and W % 2 == 0)):
+        # first VGG block in one kernel: the full-resolution 64-channel activation stays on chip
+        h, w = (H // 2, W // 2) if L0["pool"] else (H, W)
+        x = torch.empty(B, h, w, 64, dtype=torch.bfloat16, device=dev)
+        if "stem_par" not in P:  # per-channel operands of both convolutions, on the host (kernel parameters)
+            P["stem_par"] = torch.stack([P["c1a_b"], P["c1a_s"], P["c1a_t"], L0["b"], L0["s"], L0["t"]]).float().cpu()
+        ops.sp_conv_stem(image, P["c1a_w"], P["stem_par"], L0["w"], L0["pool"], x)
+        rest = P["convs"][1:]
+    else:
+        x = torch.empty(B, H, W, 64, dtype=torch.bfloat16, device=dev)
+        ops.sp_conv1a(image, P["c1a_w"], P["c1a_b"], P["c1a_s"], P["c1a_t"], x)
+        h, w = H, W
+        rest = P["convs"]
+    for L in rest:
         oh, ow = (h // 2, w // 2) if L["pool"] else (h, w)
         y = torch.empty(B, oh, ow, L["cout"], dtype=torch.bfloat16, device=dev)
         ops.gemm(x, L["w"], M=0, N=L["cout"], K=9 * L["cin"], lda=L["cin"], block_n=min(L["cout"], 256),

@@ -137,6 +137,19 @@ def sp_conv1a(image, w, bias, scale, shift, out):
                                              _ptr(out), _stream()))
 
 
+def sp_conv_stem(image, w1, host_params, w2, pool, out):
+    """First VGG block in one kernel: conv 1->64 (+ReLU+BN) -> conv 64->64 (+ReLU+BN) -> optional 2x2 max pool.
+    host_params: CPU float32 tensor [6, 64] = bias1 | scale1 | shift1 | bias2 | scale2 | shift2."""
+    _require_cuda(image, out, w2, w1)
+    if host_params.is_cuda or host_params.dtype != torch.float32 or tuple(host_params.shape) != (6, 64):
+        raise ValueError("sp_conv_stem: host_params must be a CPU float32 tensor of shape (6, 64)")
+    host_params = host_params.contiguous()
+    b, c, h, wd = image.shape
+    with _timed("sp_conv_stem", 1, 2.0 * b * h * wd * 64 * (9 + 576)):
+        _lib.check(_lib.lib().b200_sp_conv_stem(_ptr(image), b, c, h, wd, _ptr(w1), host_params.data_ptr(), _ptr(w2),
+                                                int(pool), _ptr(out), _stream()))
+
+
 def sp_nms_border(scores, radius, pad):
     _require_cuda(scores)
     b, h, w = scores.shape

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 3
+#define B200_ABI_VERSION 4
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -104,6 +104,15 @@ int b200_attention(const b200_attn_desc* d, b200_stream_t stream);
 int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* w /*[64,9]*/,
                    const float* bias, const float* scale, const float* shift, void* out_nhwc,
                    b200_stream_t stream);
+/* the whole first VGG block in one kernel (:59-75,96-105 of superpoint_open.py; conv1a / conv1b of
+ * gluefactory_nonfree/superpoint.py:166-167,276-277): conv3x3 1 -> 64 (+ReLU+BN) and conv3x3 64 -> 64 (+ReLU+BN),
+ * optional 2x2 max pool; the intermediate activation stays on chip.  w2 is the second convolution packed
+ * as bf16 [64, 9*64] (tap-major, then input channel), as b200_gemm's conv mode takes it.  host_params is
+ * a HOST array float[6][64] = bias1 | scale1 | shift1 | bias2 | scale2 | shift2: the per-channel operands travel
+ * in the kernel parameters (constant bank), so the epilogues issue no loads for them. */
+int b200_sp_conv_stem(const float* image, int B, int C, int H, int W, const float* w1 /*[64,9] device*/,
+                      const float* host_params /*[6][64] host*/, const void* w2, int pool, void* out_nhwc,
+                      b200_stream_t stream);
 /* batched_nms (:34-49) + border removal (:147-152); out has the shape of scores */
 int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
                        float* out, b200_stream_t stream);

@@ -145,6 +145,44 @@ def test_conv3x3_relu_bn_pool(dev, cin, cout, H, W, pool):
     _close(y.permute(0, 3, 1, 2), ref, 1e-2, 2e-2, "conv")
 
 
+@pytest.mark.parametrize("C,H,W,pool,B", [(1, 48, 40, 1, 2), (1, 37, 53, 0, 2), (3, 64, 24, 1, 1), (1, 16, 8, 1, 3),
+                                          (1, 200, 312, 1, 2)])
+def test_conv_stem_fused(dev, C, H, W, pool, B):
+    """conv 1->64 (+ReLU+BN) -> conv 64->64 (+ReLU+BN) -> pool in one kernel against fp32 PyTorch (with the
+    intermediate activation and the second weights rounded to bf16 as the kernel holds them) and against the
+    two-kernel CUDA path (conv1a, conv3x3)."""
+    from glue_factory_b200 import ops
+
+    img = torch.rand(B, C, H, W, device=dev, generator=torch.Generator(device=dev).manual_seed(40 + H))
+    w1 = _rand((64, 9), dev, 41, 1 / 3.0)
+    b1, s1, t1 = _rand((64,), dev, 42, 0.1), 1 + _rand((64,), dev, 43, 0.2), _rand((64,), dev, 44, 0.2)
+    w2 = _rand((64, 64, 3, 3), dev, 45, 1 / math.sqrt(9 * 64))
+    w2p = _bf(w2.permute(0, 2, 3, 1).reshape(64, -1)).contiguous()
+    b2, s2, t2 = _rand((64,), dev, 46, 0.1), 1 + _rand((64,), dev, 47, 0.2), _rand((64,), dev, 48, 0.2)
+    oh, ow = (H // 2, W // 2) if pool else (H, W)
+    y = torch.zeros(B, oh, ow, 64, dtype=torch.bfloat16, device=dev)
+    ops.sp_conv_stem(img, w1, torch.stack([b1, s1, t1, b2, s2, t2]).cpu(), w2p, pool, y)
+    # two-kernel path
+    mid = torch.empty(B, H, W, 64, dtype=torch.bfloat16, device=dev)
+    ops.sp_conv1a(img, w1, b1, s1, t1, mid)
+    y2 = torch.zeros_like(y)
+    ops.gemm(mid, w2p, M=0, N=64, K=576, lda=64, block_n=64, epilogue=ops.EPI_CONV_RELU_BN, batch=B, conv=(H, W, 64),
+             bias=b2, scale=s2, shift=t2, relu=1, pool=pool, out16=y2, ld16=64)
+    torch.cuda.synchronize()
+    gray = img if C == 1 else (img * torch.tensor([0.299, 0.587, 0.114], device=dev).view(1, 3, 1, 1)).sum(1, keepdim=True)
+    a = F.conv2d(gray, w1.view(64, 1, 3, 3), b1, padding=1)
+    a = (F.relu(a) * s1[None, :, None, None] + t1[None, :, None, None]).to(torch.bfloat16).float()
+    w_r = w2p.float().view(64, 3, 3, 64).permute(0, 3, 1, 2)
+    ref = F.conv2d(a, w_r, b2, padding=1)
+    ref = F.relu(ref) * s2[None, :, None, None] + t2[None, :, None, None]
+    if pool:
+        ref = F.max_pool2d(ref, 2, 2)
+    _close(y.permute(0, 3, 1, 2), ref, 1e-2, 2e-2, "fused stem vs fp32 reference")
+    # the two CUDA paths differ only where an intermediate value sat on a bf16 rounding boundary
+    diff = (y.float() - y2.float()).abs()
+    assert diff.max().item() <= 0.05 and (diff > 0.02).float().mean().item() < 1e-3, diff.max().item()
+
+
 def test_heads_desc_l2_and_score_softmax(dev):
     from glue_factory_b200 import ops
 
