@@ -43,7 +43,8 @@ constexpr int kStStageBytes = 128 * 64 * 2;                            // output
 constexpr int kStSmemBytes = 1024 + kStWBytes + kStPatchStages * kStPatchBytes + kStABytes + kStW1Bytes + 256 +
                              kStStageBytes + 2 * 256 * 4;
 constexpr int kStImgH = kStPatchH + 2, kStImgW = kStPatchW + 2;  // image pixels under the patch: 20 x 12
-constexpr uint32_t kStTmemCols = 256;  // [0,128): output accumulators (2 x 64)   [128,256): stem GEMM (2 M-tiles x 64)
+// [0,128): output accumulators (2 x 64)   [128,384): stem GEMM, double-buffered (2 x 2 M-tiles x 64)
+constexpr uint32_t kStTmemCols = 512;
 static_assert(kStSmemBytes <= 227 * 1024, "shared memory budget");
 
 
@@ -56,6 +57,7 @@ extern "C" int b200_debug_stem_trace(long long* dst) { return (int)cudaMemcpyFro
 #endif
 __device__ __forceinline__ void st_epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 __device__ __forceinline__ void st_work_bar() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
+__device__ __forceinline__ void st_build_bar() { asm volatile("bar.sync 3, 128;" ::: "memory"); }
 __device__ __forceinline__ uint32_t st_bf16x2_max(uint32_t a, uint32_t b) {
     uint32_t d;
     asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
@@ -78,12 +80,12 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     uint64_t* bars = reinterpret_cast<uint64_t*>(sW1 + kStW1Bytes);
     uint64_t* w_full = bars;            // second-convolution weights landed
     uint64_t* a_full = bars + 1;        // im2col rows (and, the first time, the stem weight tile) written
-    uint64_t* c1_full = bars + 2;       // stem GEMM retired
-    uint64_t* patch_full = bars + 3;    // [2] halo patch written
-    uint64_t* patch_empty = bars + 5;   // [2] the 36 MMAs reading it retired
-    uint64_t* acc_full = bars + 7;      // [2]
-    uint64_t* acc_empty = bars + 9;     // [2]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    uint64_t* c1_full = bars + 2;       // [2] stem GEMM retired (even / odd tiles)
+    uint64_t* patch_full = bars + 4;    // [2] halo patch written
+    uint64_t* patch_empty = bars + 6;   // [2] the 36 MMAs reading it retired
+    uint64_t* acc_full = bars + 8;      // [2]
+    uint64_t* acc_empty = bars + 10;    // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
     uint8_t* sStage = reinterpret_cast<uint8_t*>(bars) + 256;              // [128 px][64] bf16, swizzled
     float* sImg = reinterpret_cast<float*>(sStage + kStStageBytes);        // [2][20 x 12] gray pixels under the patch
 
@@ -94,9 +96,9 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     if (warp == 0 && lane == 0) {
         prefetch_tensormap(&tmap_w);
         mbar_init(w_full, 1);
-        mbar_init(a_full, 8);
-        mbar_init(c1_full, 1);
+        mbar_init(a_full, 4);
         for (int s = 0; s < 2; ++s) {
+            mbar_init(c1_full + s, 1);
             mbar_init(patch_full + s, 8);
             mbar_init(patch_empty + s, 1);
             mbar_init(acc_full + s, 1);
@@ -121,22 +123,25 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         const bool leader = elect_one();
         constexpr uint32_t idesc = umma_idesc(128, 64, 1u, 0u, 0u);
         const uint32_t w0 = smem_u32(sW), w1 = smem_u32(sW1), a_im = smem_u32(sA);
-        auto issue_stem = [&]() {  // conv 1 -> 64 on the 180 patch pixels: 2 M-tiles x (K = 32)
+        // conv 1 -> 64 on the 180 patch pixels: 2 M-tiles x (K = 32).  Tile parity `par` selects the im2col
+        // buffer (K columns [32 par, 32 par + 32) of the 128-byte rows) and the TMEM accumulator pair.
+        auto issue_stem = [&](int par) {
             if (leader) {
 #pragma unroll
                 for (int m = 0; m < 2; ++m)
 #pragma unroll
                     for (int k = 0; k < 2; ++k)
-                        umma_f16(tmem_base + 128 + m * 64, umma_smem_desc_sw128(a_im + m * 16384 + k * 32, 1024, 16),
+                        umma_f16(tmem_base + 128 + par * 128 + m * 64,
+                                 umma_smem_desc_sw128(a_im + m * 16384 + par * 64 + k * 32, 1024, 16),
                                  umma_smem_desc_sw128(w1 + k * 32, 1024, 16), idesc, k != 0 ? 1u : 0u);
-                umma_commit(c1_full);
+                umma_commit(c1_full + par);
             }
             __syncwarp();
         };
         if (blockIdx.x < total_tiles) {
             mbar_wait(a_full, 0);
             tc_fence_after();
-            issue_stem();
+            issue_stem(0);
         }
         mbar_wait(w_full, 0);
         int acc = 0;
@@ -148,7 +153,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                 mbar_wait(a_full, (uint32_t)((i + 1) & 1));
                 tc_fence_after();
                 if (leader) ST_T(0, i, 0);
-                issue_stem();
+                issue_stem((i + 1) & 1);
                 if (leader) ST_T(0, i, 1);
             }
             mbar_wait(patch_full + st, (uint32_t)((i >> 1) & 1));
@@ -294,16 +299,21 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             }
         };
         const long long plane = (long long)p.H * p.W;
-        // gray pixel under the patch of tile t (zero outside the image): one per thread
-        auto load_img = [&](int t) {
+        // The TMEM lane quarters 0 / 1 hold patch pixels of both M-tiles, quarters 2 / 3 only of the first one, so
+        // the warps of quarters 2 / 3 (half the TMEM -> patch work) also build the im2col rows: `bt` numbers
+        // their 128 threads.
+        const bool builder = quarter >= 2;
+        const int bt = (((warp - 6) >> 2) * 2 + (quarter - 2)) * 32 + lane;
+        // gray pixel e (of 20 x 12) under the patch of tile t, zero outside the image
+        auto load_img = [&](int t, int e) {
             const int b = t / tiles_per_img;
             const int rem = t - b * tiles_per_img;
             const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
             const float* base = p.img + (long long)b * p.C * plane;
-            const int iy = wt / kStImgW, ix = wt - iy * kStImgW;
+            const int iy = e / kStImgW, ix = e - iy * kStImgW;
             const int yy = ty * kStTileH - 2 + iy, xx = tx * kStTileW - 2 + ix;
             float v = 0.f;
-            if (wt < kStImgH * kStImgW && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+            if (e < kStImgH * kStImgW && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
                 const long long o = (long long)yy * p.W + xx;
                 if (p.C == 3) {
                     // same association order as (image * [0.299, 0.587, 0.114]).sum(1)
@@ -316,22 +326,15 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             }
             return v;
         };
-        float nxt = 0.f;
-        if (blockIdx.x < total_tiles) sImg[wt] = load_img(blockIdx.x);
-        uint32_t r[32];
-        int i = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
-            const int st = i & 1;
-            const int b = t / tiles_per_img;
-            const int rem = t - b * tiles_per_img;
-            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-            const int y0 = ty * kStTileH - 1, x0 = tx * kStTileW - 1;  // image position of patch pixel (0, 0)
-            const float* img_s = sImg + st * 256;
-            st_work_bar();  // this tile's image pixels are staged
-            if (wt == 0) ST_T(1, i, 0);
-            // ---- im2col row of patch pixel wt: [hi(9) | lo(9) | hi(9) | 0] ----
-            if (wt < kStPatchPx) {
-                const int pr = wt / kStPatchW, pc = wt - pr * kStPatchW;
+        // im2col rows of patch pixels bt, bt + 128 for the tile whose pixels are staged in img_s:
+        // [hi(9) | lo(9) | hi(9) | 0], written to K columns [32 par, 32 par + 32) of the pixel's row
+        // (chunks 4 par .. 4 par + 3 under the 128-byte swizzle)
+        auto im2col = [&](const float* img_s, int par) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int pi = bt + j * 128;
+                if (pi >= kStPatchPx) continue;
+                const int pr = pi / kStPatchW, pc = pi - pr * kStPatchW;
                 float f[32];
 #pragma unroll
                 for (int k = 27; k < 32; ++k) f[k] = 0.f;
@@ -343,21 +346,50 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                     f[9 + k] = lo;
                     f[18 + k] = hi;
                 }
-                uint8_t* row = sA + wt * 128;  // M-tile wt / 128, row wt % 128
+                uint8_t* row = sA + pi * 128;  // M-tile pi / 128, row pi % 128
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
-                    *reinterpret_cast<uint4*>(row + ((c ^ (wt & 7)) << 4)) =
+                    *reinterpret_cast<uint4*>(row + (((par * 4 + c) ^ (pi & 7)) << 4)) =
                         make_uint4(pack_bf16(f[c * 8], f[c * 8 + 1]), pack_bf16(f[c * 8 + 2], f[c * 8 + 3]),
                                    pack_bf16(f[c * 8 + 4], f[c * 8 + 5]), pack_bf16(f[c * 8 + 6], f[c * 8 + 7]));
             }
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(a_full);
+        };
+        float nxt0 = 0.f, nxt1 = 0.f;
+        if (builder && blockIdx.x < total_tiles) {
+            sImg[bt] = load_img(blockIdx.x, bt);
+            sImg[bt + 128] = load_img(blockIdx.x, bt + 128);
+            st_build_bar();
+            im2col(sImg, 0);
+            if (blockIdx.x + gridDim.x < total_tiles) {
+                nxt0 = load_img(blockIdx.x + gridDim.x, bt);
+                nxt1 = load_img(blockIdx.x + gridDim.x, bt + 128);
+            }
+        }
+        uint32_t r[32];
+        int i = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+            const int st = i & 1;
+            const int b = t / tiles_per_img;
+            const int rem = t - b * tiles_per_img;
+            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+            const int y0 = ty * kStTileH - 1, x0 = tx * kStTileW - 1;  // image position of patch pixel (0, 0)
+            if (wt == 0) ST_T(1, i, 0);
+            // ---- next tile first: its stem GEMM then runs while this tile's patch is written ----
+            if (builder && t + gridDim.x < total_tiles) {
+                sImg[(st ^ 1) * 256 + bt] = nxt0;
+                sImg[(st ^ 1) * 256 + bt + 128] = nxt1;
+                st_build_bar();  // the next tile's image pixels are staged
+                im2col(sImg + (st ^ 1) * 256, st ^ 1);
+                if (t + 2 * gridDim.x < total_tiles) {  // in flight for a whole tile
+                    nxt0 = load_img(t + 2 * gridDim.x, bt);
+                    nxt1 = load_img(t + 2 * gridDim.x, bt + 128);
+                }
+            }
             if (wt == 0) ST_T(1, i, 1);
-            const bool more = t + gridDim.x < total_tiles;
-            if (more) nxt = load_img(t + gridDim.x);  // in flight while the stem GEMM runs
-            if (wt == 0) ST_T(1, i, 5);
-            mbar_wait(c1_full, (uint32_t)(i & 1));  // stem GEMM of this tile retired (the im2col rows are free again)
+            mbar_wait(c1_full + st, (uint32_t)((i >> 1) & 1));  // stem GEMM of this tile retired
             tc_fence_after();
             if (wt == 0) ST_T(1, i, 2);
             mbar_wait(patch_empty + st, (uint32_t)(((i >> 1) & 1) ^ 1));  // the tile before last is done with the slot
@@ -371,7 +403,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                 const int pr = pi / kStPatchW, pc = pi - pr * kStPatchW;
                 const int y = y0 + pr, x = x0 + pc;
                 const bool inside = y >= 0 && y < p.H && x >= 0 && x < p.W;
-                const uint32_t taddr = tmem_base + 128 + m * 64 + ((uint32_t)(quarter * 32) << 16);
+                const uint32_t taddr = tmem_base + 128 + st * 128 + m * 64 + ((uint32_t)(quarter * 32) << 16);
                 uint8_t* dst = patch + (pr * kStPatchPitch + pc) * 128;
                 tmem_ld32(taddr + chalf * 32, r);
                 tmem_ld_wait();
@@ -392,7 +424,6 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             __syncwarp();
             if (lane == 0) mbar_arrive(patch_full + st);
             if (wt == 0) ST_T(1, i, 4);
-            if (more) sImg[(st ^ 1) * 256 + wt] = nxt;
         }
     }
     tc_fence_before();
