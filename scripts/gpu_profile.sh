@@ -11,9 +11,9 @@ cap() {  # name, regex, skip, count
   echo "capture $1 exit=$?"
 }
 for w in $WHAT; do case $w in
-  list) ncu --metrics gpu__time_duration.sum --clock-control none -s 420 -c 300 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "launch list exit=$?";;
+  list) ncu --metrics gpu__time_duration.sum --clock-control none -c 100000 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list.log 2>&1; echo "launch list exit=$?";;
   att) cap attention "attention_tcgen05" 60 1;;
   gemm) cap gemm "gemm_tcgen05" 14 8;;
-  conv) cap conv "conv_patch_kernel|conv1a_kernel|nms_list_kernel" 12 5;;
+  conv) cap conv "conv_stem_kernel|conv_patch_kernel|nms_list_kernel" 6 5;;
 esac; done
 ls -la gpurun_out | tail -8
