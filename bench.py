@@ -205,15 +205,48 @@ def run_b200(args):
         with torch.no_grad():
             return pipe(resident)
 
+    # End to end: every step copies its own inputs from pinned host memory and returns its result record to
+    # the host.  As a data loader would, the copy of step i+1 is issued on a side stream while step i computes
+    # (two device input buffers); every copy and every read-back stays inside the timed region.
+    copy_stream = torch.cuda.Stream(device=dev)
+    dev_in = [{k: torch.empty(v.shape, dtype=v.dtype, device=dev) for k, v in host.items()} for _ in range(2)]
+    copied = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    e2e_state = {"i": 0, "n": 0}
+
+    def issue_copy(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])  # the step that last read this buffer has finished with it
+            for k, v in host.items():
+                dev_in[slot][k].copy_(v, non_blocking=True)
+            copied[slot].record(copy_stream)
+
+    def e2e_begin(n):
+        e2e_state["i"], e2e_state["n"] = 0, n
+        for ev in consumed:
+            ev.record()
+
     def step_e2e():
+        i, n = e2e_state["i"], e2e_state["n"]
+        slot = i & 1
+        if i == 0:
+            issue_copy(0)
+        if i + 1 < n:
+            issue_copy(slot ^ 1)
+        main = torch.cuda.current_stream()
+        main.wait_event(copied[slot])
         with torch.no_grad():
-            pred = pipe(to_views(host["image0"].to(dev, non_blocking=True), host["image1"].to(dev, non_blocking=True),
-                                 host["size"].to(dev, non_blocking=True)))
+            d = dev_in[slot]
+            pred = pipe(to_views(d["image0"], d["image1"], d["size"]))
+        consumed[slot].record(main)
         for k in RESULT_KEYS:
             if k not in out_host:
                 out_host[k] = torch.empty(pred[k].shape, dtype=pred[k].dtype).pin_memory()
             out_host[k].copy_(pred[k], non_blocking=True)
-        torch.cuda.synchronize()  # the host reads the result record of this step
+        done = torch.cuda.Event()
+        done.record(main)
+        done.synchronize()  # the host reads the result record of this step (the prefetch keeps running)
+        e2e_state["i"] = i + 1
         return pred
 
     def barrier():
@@ -244,8 +277,11 @@ def run_b200(args):
     launches = ops.launches()
     records = list(ops.profile_records())
     ops.reset_stats(profile=False)
+    e2e_begin(2)
     for _ in range(2):
         step_e2e()
+    torch.cuda.synchronize()
+    e2e_begin(steps)
     ms_e2e = timed(step_e2e, steps, profile=False)
     d2h_bytes = sum(t.numel() * t.element_size() for t in out_host.values())
 
@@ -289,7 +325,9 @@ def run_b200(args):
                        "matcher": MATCHER_CONF, "parallelism": f"pairs sharded over {world} GPU(s), no collective in the step",
                        "l2": "inputs_exceed_l2 (268 MB of images, >10 GB of activations per step)"},
             "e2e": {"value": total_pairs / (ms_e2e * 1e-3), "unit": "pairs/s", "h2d_bytes_per_step": h2d_bytes,
-                    "d2h_bytes_per_step": d2h_bytes, "ms_per_step": ms_e2e / steps},
+                    "d2h_bytes_per_step": d2h_bytes, "ms_per_step": ms_e2e / steps,
+                    "pipelining": "step i+1's pinned-host -> device copy runs on a side stream under step i's kernels; "
+                                  "all copies and read-backs are inside the timed region"},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "tensor" if tensor_bound else "hbm", "kernel": top_tag, "achieved": achieved,

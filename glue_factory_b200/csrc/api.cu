@@ -30,8 +30,8 @@ int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const C
 int launch_conv_patch(int cout, const CUtensorMap& ta, const CUtensorMap& tw, const GemmParams& p, int num_sms,
                       cudaStream_t stream);
 int launch_conv_stem(const CUtensorMap& tw, const StemParams& p, int num_sms, cudaStream_t stream);
-int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
-                     int num_seqs, int max_q_len, int heads, cudaStream_t stream);
+int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
+                     int num_seqs, int max_q_len, int heads, int num_sms, cudaStream_t stream);
 
 // ---------------------------------------------------------------------------------------------
 // driver entry point for cuTensorMapEncodeTiled (no link-time dependency on libcuda)
@@ -244,7 +244,9 @@ int b200_attention(const b200_attn_desc* d, b200_stream_t stream_) {
     p.q_col0 = d->q_col0; p.k_col0 = d->k_col0; p.v_col0 = d->v_col0;
     p.scale = d->scale;
     p.out = d->out; p.ld_out = d->ld_out; p.out_col0 = d->out_col0;
-    return launch_attention(tq, tk, tv, p, d->num_seqs, d->max_q_len, d->heads, stream);
+    const int num_sms = sm_count();
+    B200_REQUIRE(num_sms > 0, "attention: no CUDA device available");
+    return launch_attention(tq, tk, tv, p, d->num_seqs, d->max_q_len, d->heads, num_sms, stream);
 }
 
 int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* w, const float* bias,

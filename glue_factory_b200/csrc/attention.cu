@@ -1,7 +1,10 @@
 // Dense path: flash-style multi-head attention on tcgen05 / TMEM for head_dim 64.
 //
-// One CTA per (pair of 128-query tiles, head, sequence); 1 CTA per SM (all 512 TMEM columns).
-//   warp 0       TMEM allocation + TMA producer: Q tiles once, 64-key K/V tiles through a ring of smem slots
+// Persistent CTAs (one per SM, all 512 TMEM columns) walk a list of work items; an item is a pair of
+// 128-query tiles of one (sequence, head).
+//   warp 0       TMEM allocation + TMA producer: Q tiles (double-buffered per query tile) and 64-key K/V tiles
+//                through one ring of smem slots that runs ACROSS items, so the next item's Q and first K/V
+//                tiles are on chip before the current item drains
 //   warps 1-16   four independent streams of four warps, one query row per thread; the first warp of a
 //                stream also issues the stream's tcgen05.mma (one elected lane, uniform-register operands)
 // A stream is (query tile g, key-tile parity x): it owns the even (x = 0) or odd (x = 1) 64-key tiles of
@@ -11,12 +14,14 @@
 //   running maximum and write P back over S as bf16 pairs (tcgen05.st, 32 columns)
 //   O += P V_t         tcgen05.mma with the A operand read from TMEM, V consumed token-major through an
 //                      MN-major descriptor, accumulating in TMEM (64 columns)
-//   the next S of the stream is issued right behind PV (the tensor pipe is in order, so it may overwrite P).
+//   the next S of the stream is issued right behind PV (the tensor pipe is in order, so it may overwrite P);
+//   behind the item's last PV that is already the first S of the NEXT item.
 // Nothing couples the streams inside the key loop (beyond the K/V ring): a stream waits on the tensor core
 // for about half of its tile time, and the other three streams keep the MUFU busy meanwhile (every
-// scheduler holds one warp of each stream; the streams start a quarter period apart).
-// At the end the two streams of a query tile are merged like split-KV partial results:
-//   O = (wA O_A + wB O_B) / (wA l_A + wB l_B),  w = 2^(c (m - max(mA, mB))).
+// scheduler holds one warp of each stream).
+// At the end of an item the two streams of a query tile are merged like split-KV partial results,
+//   O = (wA O_A + wB O_B) / (wA l_A + wB l_B),  w = 2^(c (m - max(mA, mB))),
+// each stream reading BOTH accumulators from TMEM for its half of the 64 output dimensions.
 // Online softmax with a lazily updated reference maximum: the running maximum m only moves (and O / the
 // row sum are rescaled, tcgen05.ld -> multiply -> tcgen05.st) when a row's new maximum exceeds it by more
 // than 2^8 in the exp2 domain; otherwise P is simply taken against the stale m (values <= 256, harmless
@@ -37,71 +42,95 @@ constexpr int kQTile = 128, kKvTile = 64, kHeadDim = 64;
 constexpr int kQPerCta = 2 * kQTile;
 constexpr int kQBytes = kQTile * kHeadDim * 2;    // 16 KB
 constexpr int kKvBytes = kKvTile * kHeadDim * 2;  // 8 KB: 64 keys x 64 bf16
-constexpr int kKvStages = 6;
-#ifndef ATT_OFFSET_NS
-#define ATT_OFFSET_NS 280
-#endif
-constexpr int kStreamOffsetNs = ATT_OFFSET_NS;  // ~ a quarter of the time four streams need for 64 keys each
-constexpr int kCombBytes = 2 * kQTile * kHeadDim * 4;  // merge buffer: [2 query tiles][128 rows][64 fp32]
-constexpr int kXchFloats = 2 * 2 * 2 * kQTile;         // [m | l][query tile][stream parity][row]
-// smem: Q[2] | K[stages] V[stages] | merge buffer | barriers | (m, l) exchange
-constexpr int kAttSmemBytes = 1024 + 2 * kQBytes + 2 * kKvStages * kKvBytes + kCombBytes + 256 + kXchFloats * 4;
+constexpr int kKvStages = 8;
+constexpr int kXchFloats = 2 * 2 * 2 * kQTile;  // [m | l][query tile][stream parity][row]
+// smem: Q[query tile][2 buffers] | K[stages] V[stages] | barriers | (m, l) exchange
+constexpr int kAttSmemBytes = 1024 + 4 * kQBytes + 2 * kKvStages * kKvBytes + 512 + kXchFloats * 4;
 // stream s = 2 g + x:  S/P_s: [64 s, 64 s + 64)   O_s: [256 + 64 s, 256 + 64 s + 64)
 constexpr uint32_t kAttTmemCols = 512;
 
 __device__ __forceinline__ float ex2_approx(float x) {
-#ifdef ATT_NOEX2
-    return x * 0.001f;
-#endif
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+
+// one work item, decoded identically by every warp (all fields warp-uniform)
+struct AttItem {
+    bool active;     // the item's first query tile holds at least one row
+    bool g1_active;  // so does the second one
+    int q_row0, kv_row0, q_len, kv_len, kv_tiles, qt, head;
+};
+
+// the four words of an item that come from memory (two dependent global loads: ~1500 clk when not hidden)
+struct AttRaw {
+    int q_row0, kv_row0, q_len, kv_len;
+};
+
+__device__ __forceinline__ AttRaw att_fetch(const AttnParams& p, int it) {
+    const AttnSeq sd = p.seqs[it / p.q_tiles / p.heads];
+    AttRaw r;
+    r.q_row0 = sd.q_row0;
+    r.kv_row0 = sd.kv_row0;
+    r.q_len = p.len_override ? p.len_override[sd.q_len_slot] : sd.q_len;
+    r.kv_len = p.len_override ? p.len_override[sd.kv_len_slot] : sd.kv_len;
+    return r;
+}
+
+__device__ __forceinline__ AttItem att_decode(const AttnParams& p, int it, const AttRaw& r) {
+    AttItem a;
+    a.qt = it % p.q_tiles;
+    a.head = (it / p.q_tiles) % p.heads;
+    a.q_len = __shfl_sync(0xffffffffu, r.q_len, 0);
+    a.kv_len = __shfl_sync(0xffffffffu, r.kv_len, 0);
+    a.q_row0 = __shfl_sync(0xffffffffu, r.q_row0, 0);
+    a.kv_row0 = __shfl_sync(0xffffffffu, r.kv_row0, 0);
+    a.active = a.qt * kQPerCta < a.q_len;
+    a.g1_active = a.qt * kQPerCta + kQTile < a.q_len;
+    a.kv_tiles = (a.kv_len + kKvTile - 1) / kKvTile;
+    return a;
+}
+
+__device__ __forceinline__ AttItem att_item(const AttnParams& p, int it) { return att_decode(p, it, att_fetch(p, it)); }
 
 __global__ void __launch_bounds__(kAttThreads, 1)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                          const __grid_constant__ CUtensorMap tmap_v, const AttnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sQ = smem;
-    uint8_t* sK = sQ + 2 * kQBytes;
+    uint8_t* sQ = smem;  // [g][buffer]
+    uint8_t* sK = sQ + 4 * kQBytes;
     uint8_t* sV = sK + kKvStages * kKvBytes;
-    float* sComb = reinterpret_cast<float*>(sV + kKvStages * kKvBytes);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(sComb) + kCombBytes);
-    uint64_t* q_full = bars;                  // [2]
-    uint64_t* kv_full = q_full + 2;           // [kKvStages]
-    uint64_t* kv_empty = kv_full + kKvStages; // [kKvStages]
-    uint64_t* s_full = kv_empty + kKvStages;  // [4]
-    uint64_t* p_ready = s_full + 4;           // [4]
-    uint64_t* o_done = p_ready + 4;           // [4]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kKvStages * kKvBytes);
+    uint64_t* q_full = bars;                   // [g * 2 + buffer]
+    uint64_t* q_empty = q_full + 4;            // [g * 2 + buffer], one arrival per stream of the query tile
+    uint64_t* kv_full = q_empty + 4;           // [kKvStages]
+    uint64_t* kv_empty = kv_full + kKvStages;  // [kKvStages], one arrival per query tile
+    uint64_t* s_full = kv_empty + kKvStages;   // [4]
+    uint64_t* p_ready = s_full + 4;            // [4]
+    uint64_t* o_done = p_ready + 4;            // [4]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 4);
-    float* xch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
+    float* xch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);
 
     // warp index / TMEM base / lengths go through a shuffle so that the compiler treats them, and the UMMA
     // operands derived from them, as warp-uniform: tcgen05.mma then issues straight from uniform registers
     // (a per-lane operand costs an ELECT / R2UR loop of ~75 clk around every MMA)
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
-    const int seq = blockIdx.z, head = blockIdx.y, qt = blockIdx.x;
-    const AttnSeq sd = p.seqs[seq];
-    const int q_len = __shfl_sync(0xffffffffu, p.len_override ? p.len_override[sd.q_len_slot] : sd.q_len, 0);
-    const int kv_len = __shfl_sync(0xffffffffu, p.len_override ? p.len_override[sd.kv_len_slot] : sd.kv_len, 0);
-    if (qt * kQPerCta >= q_len) return;  // uniform for the whole CTA, before any barrier / TMEM use
-    const int kv_tiles = (kv_len + kKvTile - 1) / kKvTile;
-    const bool g1_active = qt * kQPerCta + kQTile < q_len;  // second query tile holds at least one row
 
     if (warp == 0 && lane == 0) {
         prefetch_tensormap(&tmap_q);
         prefetch_tensormap(&tmap_k);
         prefetch_tensormap(&tmap_v);
-        for (int g = 0; g < 2; ++g) mbar_init(q_full + g, 1);
-        for (int s = 0; s < 4; ++s) {
-            mbar_init(s_full + s, 1);
-            mbar_init(p_ready + s, 4);  // one arrival per warp of the stream
-            mbar_init(o_done + s, 1);
+        for (int i = 0; i < 4; ++i) {
+            mbar_init(q_full + i, 1);
+            mbar_init(q_empty + i, 2);
+            mbar_init(s_full + i, 1);
+            mbar_init(p_ready + i, 4);  // one arrival per warp of the stream
+            mbar_init(o_done + i, 1);
         }
         for (int s = 0; s < kKvStages; ++s) {
             mbar_init(kv_full + s, 1);
-            mbar_init(kv_empty + s, g1_active ? 2 : 1);  // one commit per query tile using the K/V tile
+            mbar_init(kv_empty + s, 2);
         }
         fence_barrier_init();
     }
@@ -114,32 +143,39 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     if (warp == 0) {
         // ===================== TMA producer =====================
         const bool leader = elect_one();
-        const int col = head * kHeadDim;
-        const int qrow = sd.q_row0 + qt * kQPerCta;
-        if (leader) {
-            mbar_arrive_expect_tx(q_full, kQBytes);
-            tma_load_2d(sQ, &tmap_q, q_full, p.q_col0 + col, qrow);
-            if (g1_active) {
-                mbar_arrive_expect_tx(q_full + 1, kQBytes);
-                tma_load_2d(sQ + kQBytes, &tmap_q, q_full + 1, p.q_col0 + col, qrow + kQTile);
+        int kv_idx = 0;          // K/V tiles loaded so far (ring position)
+        int qcnt[2] = {0, 0};    // Q tiles loaded so far per query tile (buffer = count & 1)
+        for (int it = blockIdx.x; it < p.num_items; it += gridDim.x) {
+            const AttItem a = att_item(p, it);
+            if (!a.active || a.kv_tiles == 0) continue;
+            const int col = a.head * kHeadDim;
+            const int qrow = a.q_row0 + a.qt * kQPerCta;
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                if (g == 1 && !a.g1_active) continue;
+                const int slot = g * 2 + (qcnt[g] & 1);
+                mbar_wait(q_empty + slot, (uint32_t)(((qcnt[g] >> 1) & 1) ^ 1));
+                if (leader) {
+                    mbar_arrive_expect_tx(q_full + slot, kQBytes);
+                    tma_load_2d(sQ + slot * kQBytes, &tmap_q, q_full + slot, p.q_col0 + col, qrow + g * kQTile);
+                }
+                __syncwarp();
+                ++qcnt[g];
             }
-        }
-        __syncwarp();
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int t = 0; t < kv_tiles; ++t) {
-            const int row = sd.kv_row0 + t * kKvTile;
-            mbar_wait(kv_empty + stage, phase ^ 1);
-            if (leader) {
-                mbar_arrive_expect_tx(kv_full + stage, 2 * kKvBytes);
-                tma_load_2d(sK + stage * kKvBytes, &tmap_k, kv_full + stage, p.k_col0 + col, row);
-                tma_load_2d(sV + stage * kKvBytes, &tmap_v, kv_full + stage, p.v_col0 + col, row);
+            for (int t = 0; t < a.kv_tiles; ++t, ++kv_idx) {
+                const int stage = kv_idx % kKvStages;
+                const int row = a.kv_row0 + t * kKvTile;
+                mbar_wait(kv_empty + stage, (uint32_t)(((kv_idx / kKvStages) & 1) ^ 1));
+                if (leader) {
+                    mbar_arrive_expect_tx(kv_full + stage, 2 * kKvBytes);
+                    tma_load_2d(sK + stage * kKvBytes, &tmap_k, kv_full + stage, p.k_col0 + col, row);
+                    tma_load_2d(sV + stage * kKvBytes, &tmap_v, kv_full + stage, p.v_col0 + col, row);
+                }
+                __syncwarp();
             }
-            __syncwarp();
-            if (++stage == kKvStages) { stage = 0; phase ^= 1; }
         }
     } else {
-        // ============ softmax + output warps: stream (g, x), thread <-> query row ============
+        // ============ stream (g, x): softmax + MMA issue + output, thread <-> query row ============
         const int s = (warp - 1) >> 2;
         const bool issuer = ((warp - 1) & 3) == 0;  // first warp of the stream issues its MMAs
         const int g = s >> 1, x = s & 1;
@@ -148,39 +184,71 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
         const uint32_t tmem_s = tmem_base + s * 64 + lane_off;
         const uint32_t tmem_o = tmem_base + 256 + s * 64 + lane_off;
-        const int q_idx = qt * kQPerCta + g * kQTile + row;
+        const uint32_t tmem_o_other = tmem_base + 256 + (s ^ 1) * 64 + lane_off;
         const int pair_bar = 1 + g * 4 + quarter;  // named barrier shared by the row's two streams
-        if (g == 0 || g1_active) {
-            const float c = p.scale * 1.4426950408889634f;  // softmax(scale * s) via exp2
-            float m_run = -INFINITY, l_run = 0.f;
-            float sv[kKvTile];
-            uint32_t r[32];
-            constexpr uint32_t idesc_s = umma_idesc(128, 64, 1u, 0u, 0u);  // Q, K both K-major
-            constexpr uint32_t idesc_o = umma_idesc(128, 64, 1u, 0u, 1u);  // P K-major (TMEM), V MN-major
-            const bool lead_lane = elect_one();
-            auto issue_s = [&](int t) {  // S_s(t) = Q_g K_t^T; whole warp calls, one lane issues
-                const int stage = t % kKvStages;
-                mbar_wait(kv_full + stage, (t / kKvStages) & 1);
-                tc_fence_after();
-                const uint32_t aq = smem_u32(sQ + g * kQBytes), bk = smem_u32(sK + stage * kKvBytes);
-                if (lead_lane) {
+        constexpr uint32_t idesc_s = umma_idesc(128, 64, 1u, 0u, 0u);  // Q, K both K-major
+        constexpr uint32_t idesc_o = umma_idesc(128, 64, 1u, 0u, 1u);  // P K-major (TMEM), V MN-major
+        const bool lead_lane = elect_one();
+        const float c = p.scale * 1.4426950408889634f;  // softmax(scale * s) via exp2
+        // S_s = Q_g K^T for ring tile `idx` with Q buffer `qslot`; whole warp calls, one lane issues
+        auto issue_s = [&](int idx, int qslot) {
+            const int stage = idx % kKvStages;
+            mbar_wait(kv_full + stage, (uint32_t)((idx / kKvStages) & 1));
+            tc_fence_after();
+            const uint32_t aq = smem_u32(sQ + qslot * kQBytes), bk = smem_u32(sK + stage * kKvBytes);
+            if (lead_lane) {
 #pragma unroll
-                    for (int k = 0; k < kHeadDim / 16; ++k)
-                        umma_f16(tmem_base + s * 64, umma_smem_desc_sw128(aq + k * 32, 1024, 16),
-                                 umma_smem_desc_sw128(bk + k * 32, 1024, 16), idesc_s, k != 0 ? 1u : 0u);
-                    umma_commit(s_full + s);
-                }
-                __syncwarp();
-            };
-            if (issuer && x < kv_tiles) {
-                __nanosleep(s * kStreamOffsetNs);  // streams a quarter period apart
-                mbar_wait(q_full + g, 0);
-                issue_s(x);
+                for (int k = 0; k < kHeadDim / 16; ++k)
+                    umma_f16(tmem_base + s * 64, umma_smem_desc_sw128(aq + k * 32, 1024, 16),
+                             umma_smem_desc_sw128(bk + k * 32, 1024, 16), idesc_s, k != 0 ? 1u : 0u);
+                umma_commit(s_full + s);
             }
-            int n = 0;  // tiles of this stream so far
-            for (int t = x; t < kv_tiles; t += 2, ++n) {
-                const int valid = min(kKvTile, kv_len - t * kKvTile);
-                mbar_wait(s_full + s, n & 1);  // S_s(t) landed; every earlier MMA of the stream (PV too) retired
+            __syncwarp();
+        };
+        int kv_base = 0;   // ring position of the current item's first K/V tile
+        int qcnt = 0;      // Q tiles of query tile g used so far (buffer = count & 1)
+        int n_tot = 0;     // key tiles this stream has processed so far (phase of s_full / p_ready)
+        int od_a = 0, od_b = 0;  // items in which stream (g, 0) / (g, 1) accumulated (phase of o_done)
+        bool pre = false;  // the first S of the current item was issued at the end of the previous one
+        float sv[kKvTile];
+        uint32_t r[32];
+        // the memory words of the next item are requested while this item's first tile is in flight and decoded
+        // only where they are needed (pre-issue at the item's end, top of the next iteration)
+        AttRaw raw = {0, 0, 0, 0}, raw_next = {0, 0, 0, 0};
+        if (blockIdx.x < p.num_items) raw = att_fetch(p, blockIdx.x);
+        bool next_fetched = false;
+        for (int it = blockIdx.x; it < p.num_items; it += gridDim.x) {
+            if (it != (int)blockIdx.x) raw = next_fetched ? raw_next : att_fetch(p, it);
+            next_fetched = false;
+            const AttItem a = att_decode(p, it, raw);
+            if (!a.active) continue;
+            if (g == 1 && !a.g1_active) {
+                // query tile without rows: only hand the K/V tiles of this stream's parity back to the producer
+                if (issuer) {
+                    for (int t = x; t < a.kv_tiles; t += 2) {
+                        const int idx = kv_base + t;
+                        mbar_wait(kv_full + idx % kKvStages, (uint32_t)((idx / kKvStages) & 1));
+                        if (lane == 0) mbar_arrive(kv_empty + idx % kKvStages);
+                        __syncwarp();
+                    }
+                }
+                kv_base += a.kv_tiles;
+                continue;
+            }
+            const bool has_q = a.kv_tiles > 0;
+            const int qslot = g * 2 + (qcnt & 1);
+            const bool have = a.kv_tiles > x;              // this stream owns at least one key tile
+            const bool have_other = a.kv_tiles > (x ^ 1);  // so does the other stream of the query tile
+            if (issuer && have && !pre) {
+                mbar_wait(q_full + qslot, (uint32_t)((qcnt >> 1) & 1));
+                issue_s(kv_base + x, qslot);
+            }
+            pre = false;
+            float m_run = -INFINITY, l_run = 0.f;
+            int n = 0;  // tiles of this stream in this item
+            for (int t = x; t < a.kv_tiles; t += 2, ++n, ++n_tot) {
+                const int valid = min(kKvTile, a.kv_len - t * kKvTile);
+                mbar_wait(s_full + s, (uint32_t)(n_tot & 1));  // S_s(t) landed; every earlier MMA of the stream retired
                 tc_fence_after();
                 B200_TMEM_LD32F(tmem_s, sv);
                 B200_TMEM_LD32F(tmem_s + 32, sv + 32);
@@ -232,25 +300,50 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(p_ready + s);
+                if (n == 0 && it + (int)gridDim.x < p.num_items) {
+                    raw_next = att_fetch(p, it + gridDim.x);  // latency hides behind the wait for the next S
+                    next_fetched = true;
+                }
                 if (issuer) {
-                    mbar_wait(p_ready + s, n & 1);  // the four warps' P rows are in TMEM (O rescaled if it had to be)
+                    mbar_wait(p_ready + s, (uint32_t)(n_tot & 1));  // the four warps' P rows are in TMEM
                     tc_fence_after();
-                    const int stage = t % kKvStages;
+                    const int idx = kv_base + t;
+                    const int stage = idx % kKvStages;
                     const uint32_t bv = smem_u32(sV + stage * kKvBytes);
+                    const bool last = t + 2 >= a.kv_tiles;
                     if (lead_lane) {
 #pragma unroll
                         for (int k = 0; k < kKvTile / 16; ++k)
                             umma_f16_ts(tmem_base + 256 + s * 64, tmem_base + s * 64 + k * 8,
                                         umma_smem_desc_sw128(bv + k * 2048, 1024, 1024), idesc_o, (n | k) != 0 ? 1u : 0u);
                         umma_commit(kv_empty + stage);  // K_t / V_t free once this query tile's MMAs on them retire
-                        if (t + 2 >= kv_tiles) umma_commit(o_done + s);
+                        if (last) {
+                            umma_commit(o_done + s);
+                            umma_commit(q_empty + qslot);  // this stream is done with the item's Q tile
+                        }
                     }
                     __syncwarp();
-                    if (t + 2 < kv_tiles) issue_s(t + 2);  // in order behind PV: may overwrite P
+                    if (!last) {
+                        issue_s(idx + 2, qslot);  // in order behind PV: may overwrite P
+                    } else if (it + (int)gridDim.x < p.num_items) {
+                        // the next item's first S goes in right behind this item's last PV, so its start-up
+                        // (Q / K arrival, first MMA) runs under the merge below
+                        const AttItem nx = att_decode(p, it + gridDim.x, next_fetched ? raw_next : att_fetch(p, it + gridDim.x));
+                        if (nx.active && (g == 0 || nx.g1_active) && nx.kv_tiles > x) {
+                            const int nslot = g * 2 + ((qcnt + 1) & 1);
+                            mbar_wait(q_full + nslot, (uint32_t)(((qcnt + 1) >> 1) & 1));
+                            issue_s(kv_base + a.kv_tiles + x, nslot);
+                            pre = true;
+                        }
+                    }
                 }
             }
-            // ---- merge the row's two streams: O = (wA O_A + wB O_B) / (wA l_A + wB l_B) ----
-            const bool have = n > 0;
+            if (issuer && has_q && !have) {  // no key tile for this stream: it still releases the Q tile
+                if (lane == 0) mbar_arrive(q_empty + qslot);
+                __syncwarp();
+            }
+            // ---- merge the row's two streams: O = (wA O_A + wB O_B) / (wA l_A + wB l_B); this stream writes
+            //      output dimensions [32 x, 32 x + 32) ----
             float* xm = xch + ((g * 2 + x) * kQTile + row);
             float* xo = xch + ((g * 2 + (x ^ 1)) * kQTile + row);
             xm[0] = m_run;
@@ -259,57 +352,51 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
             const float m_o = xo[0], l_o = xo[4 * kQTile];
             const float m_all = fmaxf(m_run, m_o);
             const float w_me = have ? ex2_approx((m_run - m_all) * c) : 0.f;
-            const float w_o = l_o > 0.f ? ex2_approx((m_o - m_all) * c) : 0.f;
+            const float w_o = have_other ? ex2_approx((m_o - m_all) * c) : 0.f;
             const float l_all = l_run * w_me + l_o * w_o;
-            const float f = l_all > 0.f ? w_me / l_all : 0.f;  // no keys: zeros
+            const float inv = l_all > 0.f ? 1.0f / l_all : 0.f;  // no keys: zeros
+            const float f_me = w_me * inv, f_o = w_o * inv;
             if (have) {
-                mbar_wait(o_done + s, 0);  // the stream's last PV has landed in O_s
+                mbar_wait(o_done + s, (uint32_t)((x == 0 ? od_a : od_b) & 1));  // the stream's last PV has landed
                 tc_fence_after();
             }
-            float4* comb = reinterpret_cast<float4*>(sComb) + (g * kQTile + row) * 16;
-            if (x == 1) {
-#pragma unroll
-                for (int ch = 0; ch < 2; ++ch) {
-                    if (have) {
-                        tmem_ld32(tmem_o + ch * 32, r);
-                        tmem_ld_wait();
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (have)
-                            v = make_float4(__uint_as_float(r[4 * i]) * f, __uint_as_float(r[4 * i + 1]) * f,
-                                            __uint_as_float(r[4 * i + 2]) * f, __uint_as_float(r[4 * i + 3]) * f);
-                        comb[(ch * 8 + i) ^ (row & 15)] = v;
-                    }
-                }
-                asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-            } else {
-                asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                     (long long)(sd.q_row0 + q_idx) * p.ld_out + p.out_col0 + head * kHeadDim;
-#pragma unroll
-                for (int ch = 0; ch < 2; ++ch) {
-                    if (have) {
-                        tmem_ld32(tmem_o + ch * 32, r);
-                        tmem_ld_wait();
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) r[i] = 0u;
-                    }
-                    if (q_idx < q_len) {
-#pragma unroll
-                        for (int i = 0; i < 8; i += 2) {
-                            const float4 a = comb[(ch * 8 + i) ^ (row & 15)], b = comb[(ch * 8 + i + 1) ^ (row & 15)];
-                            *reinterpret_cast<uint4*>(dst + ch * 32 + i * 4) = make_uint4(
-                                pack_bf16(__uint_as_float(r[4 * i]) * f + a.x, __uint_as_float(r[4 * i + 1]) * f + a.y),
-                                pack_bf16(__uint_as_float(r[4 * i + 2]) * f + a.z, __uint_as_float(r[4 * i + 3]) * f + a.w),
-                                pack_bf16(__uint_as_float(r[4 * i + 4]) * f + b.x, __uint_as_float(r[4 * i + 5]) * f + b.y),
-                                pack_bf16(__uint_as_float(r[4 * i + 6]) * f + b.z, __uint_as_float(r[4 * i + 7]) * f + b.w));
-                        }
-                    }
-                }
+            if (have_other) {
+                mbar_wait(o_done + (s ^ 1), (uint32_t)((x == 0 ? od_b : od_a) & 1));
+                tc_fence_after();
             }
+            float o[32];
+            if (have) {
+                tmem_ld32(tmem_o + x * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]) * f_me;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = 0.f;
+            }
+            if (have_other) {
+                tmem_ld32(tmem_o_other + x * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[i] = fmaf(__uint_as_float(r[i]), f_o, o[i]);
+            }
+            const int q_idx = a.qt * kQPerCta + g * kQTile + row;
+            if (q_idx < a.q_len) {
+                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                                     (long long)(a.q_row0 + q_idx) * p.ld_out + p.out_col0 + a.head * kHeadDim + x * 32;
+#pragma unroll
+                for (int i = 0; i < 32; i += 8)
+                    *reinterpret_cast<uint4*>(dst + i) =
+                        make_uint4(pack_bf16(o[i], o[i + 1]), pack_bf16(o[i + 2], o[i + 3]),
+                                   pack_bf16(o[i + 4], o[i + 5]), pack_bf16(o[i + 6], o[i + 7]));
+            }
+            tc_fence_before();
+            // both streams have read both accumulators (and the exchange slots): the next item may overwrite them
+            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+            kv_base += a.kv_tiles;
+            if (has_q) ++qcnt;
+            if (a.kv_tiles > 0) ++od_a;
+            if (a.kv_tiles > 1) ++od_b;
         }
     }
     tc_fence_before();
@@ -317,8 +404,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     if (warp == 0) tmem_dealloc<kAttTmemCols>(tmem_base);
 }
 
-int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const AttnParams& p,
-                     int num_seqs, int max_q_len, int heads, cudaStream_t stream) {
+int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
+                     int num_seqs, int max_q_len, int heads, int num_sms, cudaStream_t stream) {
     static bool configured = false;
     if (!configured) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -326,7 +413,12 @@ int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtenso
         configured = true;
     }
     if (num_seqs == 0 || max_q_len == 0) return 0;
-    dim3 grid((max_q_len + kQPerCta - 1) / kQPerCta, heads, num_seqs);
+    p.q_tiles = (max_q_len + kQPerCta - 1) / kQPerCta;
+    p.heads = heads;
+    const long long items = (long long)p.q_tiles * heads * num_seqs;
+    B200_REQUIRE(items < (1ll << 31), "attention: too many work items");
+    p.num_items = (int)items;
+    const int grid = (int)(items < num_sms ? items : num_sms);
     attention_tcgen05_kernel<<<grid, kAttThreads, kAttSmemBytes, stream>>>(tq, tk, tv, p);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

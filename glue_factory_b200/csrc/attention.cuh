@@ -21,6 +21,8 @@ struct AttnParams {
     void* out;                   // bf16 [tokens, ld_out]
     long long ld_out;
     int out_col0;
+    // filled by the launcher: work items = (pair of query tiles, head, sequence)
+    int q_tiles, heads, num_items;
 };
 
 }  // namespace b200

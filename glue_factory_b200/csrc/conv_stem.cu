@@ -48,13 +48,6 @@ constexpr uint32_t kStTmemCols = 512;
 static_assert(kStSmemBytes <= 227 * 1024, "shared memory budget");
 
 
-#ifdef STEM_TRACE
-__device__ long long g_stem_trace[3][8][8];
-#define ST_T(role, i, slot) do { if (blockIdx.x == 5 && (i) >= 10 && (i) < 18) g_stem_trace[role][(i) - 10][slot] = clock64(); } while (0)
-extern "C" int b200_debug_stem_trace(long long* dst) { return (int)cudaMemcpyFromSymbol(dst, g_stem_trace, sizeof(g_stem_trace)); }
-#else
-#define ST_T(role, i, slot) do {} while (0)
-#endif
 __device__ __forceinline__ void st_epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 __device__ __forceinline__ void st_work_bar() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 __device__ __forceinline__ void st_build_bar() { asm volatile("bar.sync 3, 128;" ::: "memory"); }
@@ -152,15 +145,11 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             if (t + gridDim.x < total_tiles) {  // stem GEMM of the next tile first: its workers are waiting
                 mbar_wait(a_full, (uint32_t)((i + 1) & 1));
                 tc_fence_after();
-                if (leader) ST_T(0, i, 0);
                 issue_stem((i + 1) & 1);
-                if (leader) ST_T(0, i, 1);
             }
             mbar_wait(patch_full + st, (uint32_t)((i >> 1) & 1));
-            if (leader) ST_T(0, i, 2);
             mbar_wait(acc_empty + acc, acc_phase ^ 1);
             tc_fence_after();
-            if (leader) ST_T(0, i, 3);
             const uint32_t d_tmem = tmem_base + acc * 64;
             const uint32_t a0 = smem_u32(sPatch + st * kStPatchBytes);
             if (leader) {
@@ -176,7 +165,6 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                 }
                 umma_commit(patch_empty + st);
                 umma_commit(acc_full + acc);
-                ST_T(0, i, 4);
             }
             __syncwarp();
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -199,7 +187,6 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
             mbar_wait(acc_full + acc, acc_phase);
             tc_fence_after();
-            if (et == 0) ST_T(2, (t - blockIdx.x) / gridDim.x, 0);
             const uint32_t taddr = tmem_base + acc * 64 + ((uint32_t)(quarter * 32) << 16);
             uint8_t* my_row = sStage + r_in_tile * 128;
 #pragma unroll
@@ -256,7 +243,6 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                     *reinterpret_cast<uint4*>(p.out + (((long long)b * OH + py) * OW + px) * 64 + ch * 8) = v;
                 }
             }
-            if (et == 0) ST_T(2, (t - blockIdx.x) / gridDim.x, 1);
             st_epi_bar();  // staging tile is rewritten by the next tile
         }
     } else {
@@ -376,7 +362,6 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             const int rem = t - b * tiles_per_img;
             const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
             const int y0 = ty * kStTileH - 1, x0 = tx * kStTileW - 1;  // image position of patch pixel (0, 0)
-            if (wt == 0) ST_T(1, i, 0);
             // ---- next tile first: its stem GEMM then runs while this tile's patch is written ----
             if (builder && t + gridDim.x < total_tiles) {
                 sImg[(st ^ 1) * 256 + bt] = nxt0;
@@ -388,13 +373,10 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                     nxt1 = load_img(t + 2 * gridDim.x, bt + 128);
                 }
             }
-            if (wt == 0) ST_T(1, i, 1);
             mbar_wait(c1_full + st, (uint32_t)((i >> 1) & 1));  // stem GEMM of this tile retired
             tc_fence_after();
-            if (wt == 0) ST_T(1, i, 2);
             mbar_wait(patch_empty + st, (uint32_t)(((i >> 1) & 1) ^ 1));  // the tile before last is done with the slot
             // ---- TMEM -> bias -> ReLU -> BN -> bf16 -> halo patch (zeros outside the image) ----
-            if (wt == 0) ST_T(1, i, 3);
             uint8_t* patch = sPatch + st * kStPatchBytes;
 #pragma unroll
             for (int m = 0; m < 2; ++m) {
@@ -407,7 +389,6 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                 uint8_t* dst = patch + (pr * kStPatchPitch + pc) * 128;
                 tmem_ld32(taddr + chalf * 32, r);
                 tmem_ld_wait();
-                if (wt == 0 && m == 0) ST_T(1, i, 6);
                 uint32_t pk[16];
                 if (chalf == 0) stem_affine(std::integral_constant<int, 0>{}, r, inside, pk);
                 else stem_affine(std::integral_constant<int, 1>{}, r, inside, pk);
@@ -417,13 +398,11 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                         *reinterpret_cast<uint4*>(dst + (((chalf * 4 + q) ^ (pc & 7)) << 4)) =
                             make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]);
                 }
-                if (wt == 0 && m == 0) ST_T(1, i, 7);
             }
             tc_fence_before();
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(patch_full + st);
-            if (wt == 0) ST_T(1, i, 4);
         }
     }
     tc_fence_before();

@@ -49,11 +49,10 @@ h = _lib.lib()
 if hasattr(h, "b200_debug_attention_trace"):
     import numpy as np
 
-    buf = np.zeros((2, 16, 8), dtype=np.int64)
+    buf = np.zeros((4, 8, 8), dtype=np.int64)
     h.b200_debug_attention_trace(ctypes.c_void_p(buf.ctypes.data))
     t0 = buf[0, 0, 0]
-    print("issuer, key tiles 8..23: [S g0, -, S g1, -, PV g0, -, PV g1, -]; softmax g0 warp 0: [S seen, in regs, max, exps, P stored]")
-    for j in range(16):
-        a = (buf[0, j] - t0)[[0, 2, 4, 6]].tolist()
-        b = (buf[1, j, :5] - t0).tolist()
-        print(j + 8, a, b)
+    print("per stream, items 3..10 of CTA 5: [item start, first S seen, last S seen, loop done, pair met, O ready, merge done]")
+    for st in range(4):
+        for j in range(8):
+            print(st, j + 3, (buf[st, j, :7] - t0).tolist())
