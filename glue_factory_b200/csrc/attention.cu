@@ -55,6 +55,23 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
+// 2^x on the FMA pipe (Cody-Waite: round to nearest integer through the 1.5 * 2^23 trick, degree-3 polynomial
+// on [-0.5, 0.5], exponent added as an integer): relative error <= 7.5e-5, far below the bf16 rounding of P.
+// The exponentials bound this kernel on the 16-lane MUFU; a fraction of them (ATT_POLY_PER_64 of every 64) takes
+// this path so that MUFU and issue slots are both kept busy.
+#ifndef ATT_POLY_PER_64
+#define ATT_POLY_PER_64 4
+#endif
+__device__ __forceinline__ float ex2_poly(float x) {
+    x = fmaxf(x, -125.0f);
+    const float t = x + 12582912.0f;
+    const float f = x - (t - 12582912.0f);
+    float q = fmaf(f, 0.05517173558473587f, 0.2426111251115799f);
+    q = fmaf(q, f, 0.6932609677314758f);
+    q = fmaf(q, f, 0.9999280571937561f);
+    return __int_as_float(__float_as_int(q) + (__float_as_int(t) << 23));
+}
+
 // one work item, decoded identically by every warp (all fields warp-uniform)
 struct AttItem {
     bool active;     // the item's first query tile holds at least one row
@@ -288,8 +305,10 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 float l0 = 0.f, l1 = 0.f;
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {  // column i of the P row = keys (2i, 2i+1) as bf16
+                    constexpr int kPolyStride = ATT_POLY_PER_64 > 0 ? 32 / ATT_POLY_PER_64 : 64;
+                    const bool poly = ATT_POLY_PER_64 > 0 && (i % kPolyStride) == kPolyStride - 1;
                     const float e0 = ex2_approx(fmaf(sv[2 * i], c, -mc));
-                    const float e1 = ex2_approx(fmaf(sv[2 * i + 1], c, -mc));
+                    const float e1 = poly ? ex2_poly(fmaf(sv[2 * i + 1], c, -mc)) : ex2_approx(fmaf(sv[2 * i + 1], c, -mc));
                     l0 += e0;
                     l1 += e1;
                     r[i] = pack_bf16(e0, e1);
