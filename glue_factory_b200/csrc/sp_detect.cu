@@ -20,7 +20,7 @@
 namespace b200 {
 
 constexpr int kEW = 128, kEH = 96, kSeg = 16;
-constexpr int kNmsFastThreads = 256;
+constexpr int kNmsFastThreads = 512;
 constexpr int kMaskWords = 6;  // [guard | 4 words = 128 columns | guard]
 
 __device__ __forceinline__ uint32_t order_key32(float v) {
