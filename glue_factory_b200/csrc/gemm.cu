@@ -99,6 +99,28 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
     uint32_t r[32];
     const bool has_bias = p.bias != nullptr;
     const long long row_base = (long long)batch * p.M;
+    // residual / rotary operands of one 32-column chunk: 8 row groups x 16 B per lane.  They are requested one
+    // chunk ahead (while the previous chunk is converted and stored), so their L2 / HBM latency is off the
+    // per-chunk critical path; out32 may alias resid, but only within the same chunk (same columns), and
+    // there the loads still precede the stores.
+    float4 aux[8], aux_next[8];
+    auto load_aux = [&](int c, float4 (&dst)[8]) {
+        const int col0 = n0 + c * 32;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const long long row_in_batch = tile_row0 + it * 4 + (lane >> 3);
+            const int col = col0 + (lane & 7) * 4;
+            dst[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c < BLOCK_N / 32 && col0 < p.N && row_in_batch < p.M) {
+                const long long grow = row_base + row_in_batch;
+                if constexpr (EPI == EPI_RESID)
+                    dst[it] = *reinterpret_cast<const float4*>(p.resid + grow * p.ld32 + col);
+                else if (col0 < p.rot_cols)
+                    dst[it] = __ldg(reinterpret_cast<const float4*>(p.cs + grow * 32 + ((col & 63) >> 1)));
+            }
+        }
+    };
+    if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(half, aux);
 #pragma unroll 1
     for (int c = half; c < BLOCK_N / 32; c += 2) {
         const int col0 = n0 + c * 32;
@@ -121,24 +143,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
             *reinterpret_cast<float4*>(myrow + ((q ^ (lane & 7)) << 4)) = v;
         }
         __syncwarp();
-        // residual / rotary operands of all 8 row groups first (out32 may alias resid: keep the loads ahead
-        // of the stores so that eight 128-byte row segments are in flight per warp)
-        float4 aux[8];
-        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) {
-#pragma unroll
-            for (int it = 0; it < 8; ++it) {
-                const long long row_in_batch = tile_row0 + it * 4 + (lane >> 3);
-                const int col = col0 + (lane & 7) * 4;
-                aux[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (row_in_batch < p.M) {
-                    const long long grow = row_base + row_in_batch;
-                    if constexpr (EPI == EPI_RESID)
-                        aux[it] = *reinterpret_cast<const float4*>(p.resid + grow * p.ld32 + col);
-                    else if (col0 < p.rot_cols)
-                        aux[it] = __ldg(reinterpret_cast<const float4*>(p.cs + grow * 32 + ((col & 63) >> 1)));
-                }
-            }
-        }
+        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(c + 2, aux_next);  // next chunk of this warp
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int rr = it * 4 + (lane >> 3), cj = lane & 7;
@@ -177,6 +182,10 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
                 __nv_bfloat16* o16 = reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col;
                 *reinterpret_cast<uint2*>(o16) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
             }
+        }
+        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) aux[it] = aux_next[it];
         }
         __syncwarp();
     }
