@@ -24,8 +24,7 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = one 128-byte swizzle row
 constexpr int kTileH = 8, kTileW = 16;  // conv M-tile: 8 x 16 pixels
 // epilogue warps: two per TMEM lane quarter (interleaved 32-column chunks); four per quarter for the
-// LayerNorm + GELU epilogue, which is latency-bound per warp and cannot overlap the MMA (its 128 x 512 fp32
-// accumulator fills the TMEM), so it needs the extra warps to keep the schedulers busy
+// LayerNorm + GELU epilogue, which is instruction-latency-bound per warp
 constexpr int kEpiWarps = 8;
 constexpr int kEpiWarpsLn = 16;
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == EPI_LN_GELU ? kEpiWarpsLn : kEpiWarps; }
@@ -34,7 +33,7 @@ constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged i
 constexpr int kStageBytesPerWarp = 4096;  // 32 rows x 128 B staging per epilogue warp
 constexpr int kStageBytesPerWarpLn = 2048;  // 32 rows x 64 B in the LayerNorm + GELU epilogue
 static_assert(kEpiWarps * kStageBytesPerWarp == kEpiWarpsLn * kStageBytesPerWarpLn, "one staging area for both layouts");
-constexpr int kEpiSmemBytes = kParamFloats * 4 + kEpiWarps * kStageBytesPerWarp + 128 * 4 * 8;
+constexpr int kEpiSmemBytes = kParamFloats * 4 + kEpiWarps * kStageBytesPerWarp + 2 * 128 * 4 * 8;
 
 template <int BLOCK_N>
 struct GemmCfg {
@@ -84,7 +83,7 @@ struct EpiSmem {
     const float* par1;    // [768] scale / LayerNorm gamma
     const float* par2;    // [768] shift / LayerNorm beta
     uint8_t* stage;       // this warp's 4 KB staging tile
-    float2* exch;         // [2][128] per-row partial statistics exchanged between the two column halves
+    float2* exch;         // [2][4][128] per-row partial statistics of the four column groups (two tiles in flight)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -191,45 +190,39 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
     }
 }
 
-// Linear(512 -> 512) -> LayerNorm(512) -> GELU(erf): the whole row sits in TMEM (BLOCK_N = 512).
-__device__ __forceinline__ void epilogue_ln_gelu(const GemmParams& p, const EpiSmem& es, uint32_t acc_taddr,
-                                                 long long tile_row0, int quarter, int half, int lane) {
+// Linear(512 -> 512) -> LayerNorm(512) -> GELU(erf).  The row is computed as two 256-column halves, one per
+// TMEM accumulator stage, so that the MMAs of the next row tile's first half run under the second half of this
+// epilogue (a single 128 x 512 fp32 accumulator would fill the TMEM and serialise MMA and epilogue).
+// `grp` (0..3) = this warp's column group inside a half: chunks grp and grp + 4 of the half's eight.
+__device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_taddr, int col_base, int grp,
+                                              float& sum, float& sumsq) {
     uint32_t r[32];
-    float sum = 0.f, sumsq = 0.f;
 #pragma unroll 1
-    for (int c = half; c < 16; c += 4) {
-        tmem_ld32(acc_taddr + c * 32, r);
+    for (int c = grp; c < 8; c += 4) {
+        tmem_ld32(half_taddr + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-            const float4 b = *reinterpret_cast<const float4*>(es.bias + c * 32 + q * 4);
+            const float4 b = *reinterpret_cast<const float4*>(es.bias + col_base + c * 32 + q * 4);
             const float x0 = __uint_as_float(r[q * 4]) + b.x, x1 = __uint_as_float(r[q * 4 + 1]) + b.y;
             const float x2 = __uint_as_float(r[q * 4 + 2]) + b.z, x3 = __uint_as_float(r[q * 4 + 3]) + b.w;
             sum += (x0 + x1) + (x2 + x3);
             sumsq = fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, fmaf(x3, x3, sumsq))));
         }
     }
-    const int row = quarter * 32 + lane;
-    es.exch[half * 128 + row] = make_float2(sum, sumsq);
-    epi_bar_sync<kEpiWarpsLn>();
-#pragma unroll
-    for (int o = 1; o < 4; ++o) {  // the row's other three column groups
-        const float2 other = es.exch[((half + o) & 3) * 128 + row];
-        sum += other.x;
-        sumsq += other.y;
-    }
-    const float mean = sum * (1.0f / 512.f);
-    const float var = fmaxf(sumsq * (1.0f / 512.f) - mean * mean, 0.f);
-    const float rstd = rsqrtf(var + p.ln_eps);
-    const float nmr = -mean * rstd;
+}
+
+__device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem& es, uint32_t half_taddr, int col_base,
+                                             long long tile_row0, int grp, int lane, float rstd, float nmr) {
+    uint32_t r[32];
 #pragma unroll 1
-    for (int c = half; c < 16; c += 4) {
-        tmem_ld32(acc_taddr + c * 32, r);
+    for (int c = grp; c < 8; c += 4) {
+        tmem_ld32(half_taddr + c * 32, r);
         tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-            const int col = c * 32 + q * 4;
+            const int col = col_base + c * 32 + q * 4;
             const float4 b = *reinterpret_cast<const float4*>(es.bias + col);
             const float4 g = *reinterpret_cast<const float4*>(es.par1 + col);
             const float4 be = *reinterpret_cast<const float4*>(es.par2 + col);
@@ -253,11 +246,11 @@ __device__ __forceinline__ void epilogue_ln_gelu(const GemmParams& p, const EpiS
             const uint4 v = *reinterpret_cast<const uint4*>(es.stage + rr * 64 + ((cj ^ ((rr >> 1) & 3)) << 4));
             const long long grow = tile_row0 + rr;
             if (grow < p.M)
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + c * 32 + cj * 8) = v;
+                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col_base + c * 32 +
+                                          cj * 8) = v;
         }
         __syncwarp();
     }
-    epi_bar_sync<kEpiWarpsLn>();  // exch is rewritten by the next tile
 }
 
 // thread-per-row epilogues of the SuperPoint convolutions / heads (per-column operands from smem)
@@ -413,7 +406,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
 
     const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
-    const int n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
+    // LayerNorm epilogue: a tile is a full 512-column row block, produced as kHalves column halves by the same CTA
+    constexpr int kHalves = EPI == EPI_LN_GELU ? 2 : 1;
+    const int n_tiles = EPI == EPI_LN_GELU ? 1 : (p.N + BLOCK_N - 1) / BLOCK_N;
     const long long total_tiles = (long long)p.batch * m_tiles * n_tiles;
     const int k_blocks = p.K / kBlockK;
 
@@ -447,7 +442,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const long long rest = t / n_tiles;
             const int mt = (int)(rest % m_tiles);
             const int b = (int)(rest / m_tiles);
-            const int brow = b * p.b_batch_rows + nt * BLOCK_N;
+            for (int hh = 0; hh < kHalves; ++hh) {
+            const int brow = b * p.b_batch_rows + (nt * kHalves + hh) * BLOCK_N;
             for (int kb = 0; kb < k_blocks; ++kb) {
                 mbar_wait(empty_bar + stage, phase ^ 1);
                 uint8_t* sa = smem + stage * Cfg::kStageBytes;
@@ -471,6 +467,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 __syncwarp();
                 if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
             }
+            }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
@@ -482,6 +479,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         int acc = 0;
         uint32_t acc_phase = 0;
         for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+            for (int hh = 0; hh < kHalves; ++hh) {
             mbar_wait(acc_empty + acc, acc_phase ^ 1);
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + acc * Cfg::kAccStride;
@@ -509,6 +507,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             if (leader) umma_commit(acc_full + acc);
             __syncwarp();
             if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+            }
         }
     } else {
         // ===================== epilogue warps (TMEM lanes 32*(warp%4) ..) =====================
@@ -540,13 +539,48 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const long long rest = t / n_tiles;
             const int mt = (int)(rest % m_tiles);
             const int b = (int)(rest / m_tiles);
+            if constexpr (EPI == EPI_LN_GELU) {
+                // accumulator stage h holds columns [256 h, 256 h + 256) of this row tile; both stages turn over once
+                // per tile, so one phase bit serves both.  `half` is this warp's column group (0..3) here.
+                static_assert(Cfg::kAccStages == 2 && Cfg::kAccStride == 256, "LayerNorm epilogue: two 256-column halves");
+                const uint32_t lane_taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+                const long long row0 = (long long)mt * kBlockM + quarter * 32;
+                float sum = 0.f, sumsq = 0.f;
+                mbar_wait(acc_full + 0, acc_phase);
+                tc_fence_after();
+                ln_stats_half(es, lane_taddr, 0, half, sum, sumsq);
+                mbar_wait(acc_full + 1, acc_phase);
+                tc_fence_after();
+                ln_stats_half(es, lane_taddr + 256, 256, half, sum, sumsq);
+                float2* exch = es.exch + (acc_phase & 1) * 512;
+                exch[half * 128 + r_in_tile] = make_float2(sum, sumsq);
+                epi_bar_sync<kEpiWarpsLn>();
+#pragma unroll
+                for (int o = 1; o < 4; ++o) {  // the row's other three column groups
+                    const float2 other = exch[((half + o) & 3) * 128 + r_in_tile];
+                    sum += other.x;
+                    sumsq += other.y;
+                }
+                const float mean = sum * (1.0f / 512.f);
+                const float var = fmaxf(sumsq * (1.0f / 512.f) - mean * mean, 0.f);
+                const float rstd = rsqrtf(var + p.ln_eps);
+                const float nmr = -mean * rstd;
+                ln_gelu_half(p, es, lane_taddr, 0, row0, half, lane, rstd, nmr);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(acc_empty + 0);  // the next tile's first half starts under our second half
+                ln_gelu_half(p, es, lane_taddr + 256, 256, row0, half, lane, rstd, nmr);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(acc_empty + 1);
+                acc_phase ^= 1;
+                continue;
+            }
             mbar_wait(acc_full + acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + ((uint32_t)(quarter * 32) << 16);
             if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_QKV_ROTARY || EPI == EPI_RESID || EPI == EPI_F32) {
                 epilogue_rows<BLOCK_N, EPI>(p, es, taddr, b, (long long)mt * kBlockM + quarter * 32, half, nt * BLOCK_N, lane);
-            } else if constexpr (EPI == EPI_LN_GELU) {
-                epilogue_ln_gelu(p, es, taddr, (long long)mt * kBlockM + quarter * 32, quarter, half, lane);
             } else {
                 long long row_in_batch = 0;
                 bool row_valid;
@@ -587,7 +621,7 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
         configured = true;
     }
     const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
-    const int n_tiles = (p.N + BLOCK_N - 1) / BLOCK_N;
+    const int n_tiles = EPI == EPI_LN_GELU ? 1 : (p.N + BLOCK_N - 1) / BLOCK_N;  // LayerNorm: one CTA per row tile
     const long long total = (long long)p.batch * m_tiles * n_tiles;
     if (total == 0) return 0;
     const int grid = (int)(total < num_sms ? total : num_sms);
@@ -604,7 +638,8 @@ int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const C
     B200_CASE(128, EPI_BIAS_BF16, 0)
     B200_CASE(256, EPI_BIAS_BF16, 0)
     B200_CASE(256, EPI_QKV_ROTARY, 0)
-    B200_CASE(512, EPI_LN_GELU, 0)
+    if (block_n == 512 && epi == EPI_LN_GELU && a_mode == 0)  // 512 columns as two 256-column accumulator halves
+        return launch_one<256, EPI_LN_GELU, 0>(ta, tb, p, num_sms, stream);
     B200_CASE(256, EPI_RESID, 0)
     B200_CASE(128, EPI_F32, 0)
     B200_CASE(256, EPI_F32, 0)
