@@ -337,7 +337,7 @@ def run_b200(args):
             "pipeline": {"tflops": GFLOP_PER_PAIR * value / world / 1e3, "frac_of_sustained_peak":
                          GFLOP_PER_PAIR * value / world / 1e3 / pk["tf_sustained"]},
             "kernels": [{"tag": t, "ms_per_step": v[0] / steps, "launches_per_step": v[1] / steps,
-                         "rate": v[2] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None} for t, v in ranked[:12]],
+                         "rate": v[2] / (v[0] * 1e-3) / 1e12 if v[0] > 0 else None} for t, v in ranked[:16]],
             "gather_ms": gather_ms,
         }
         if world == 1 and not args.no_cpu_baseline:

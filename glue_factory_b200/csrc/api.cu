@@ -342,6 +342,19 @@ int b200_sg_split_hilo(const float* x, long long rows, long long split_row, void
     B200_REQUIRE(x && out, "split_hilo: null argument");
     return launch_sg_split_hilo(x, rows, split_row, out, static_cast<cudaStream_t>(stream));
 }
+int b200_split_hilo(const float* x, long long rows, int cols, long long split_row, void* out, b200_stream_t stream) {
+    B200_REQUIRE(x && out, "split_hilo: null argument");
+    return launch_split_hilo(x, rows, cols, split_row, out, static_cast<cudaStream_t>(stream));
+}
+size_t b200_nn_match_workspace(int B, int M, int N) { return nn_match_workspace_bytes(B, M, N); }
+int b200_nn_match(const float* sim, int B, int M, int N, float ratio_thresh_sq, float distance_thresh_sq, int mutual_check,
+                  void* workspace, float* log_assignment, long long* matches0, long long* matches1, float* mscores0,
+                  float* mscores1, b200_stream_t stream) {
+    B200_REQUIRE(sim && workspace && log_assignment && matches0 && matches1 && mscores0 && mscores1,
+                 "nn_match: null argument");
+    return launch_nn_match(sim, B, M, N, ratio_thresh_sq, distance_thresh_sq, mutual_check, workspace, log_assignment,
+                           matches0, matches1, mscores0, mscores1, static_cast<cudaStream_t>(stream));
+}
 size_t b200_sg_sinkhorn_workspace(int B, int M, int N) { return sinkhorn_workspace_bytes(B, M, N); }
 int b200_sg_sinkhorn_assignment(const float* cost, const float* bin_score, int B, int M, int N, int iters,
                                 float filter_threshold, void* workspace, float* scores, long long* matches0,

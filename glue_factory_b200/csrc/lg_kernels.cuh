@@ -16,6 +16,9 @@ int launch_assignment(const float* sim, const float* z0, const float* z1, int B,
 int launch_assignment_finalize(const float* sim, float simw, int B, int M, int N, float threshold, void* workspace,
                                float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
                                cudaStream_t stream);
+size_t nn_match_workspace_bytes(int B, int M, int N);
+int launch_nn_match(const float* sim, int B, int M, int N, float ratio_sq, float dist_sq, int mutual, void* workspace,
+                    float* scores, long long* m0, long long* m1, float* ms0, float* ms1, cudaStream_t stream);
 void assignment_terms(void* workspace, int B, int M, int N, float** rowterm, float** colterm);
 // SuperGlue: log-domain Sinkhorn + mutual-NN filter (sg_sinkhorn.cu)
 size_t sinkhorn_workspace_bytes(int B, int M, int N);
@@ -24,6 +27,7 @@ int launch_sinkhorn_assignment(const float* cost, const float* bin_score, int B,
                                float* ms0, float* ms1, cudaStream_t stream);
 int launch_sg_kenc_head(const float* kpts, const float* scores, const float* size, int B, int n, const float* w1,
                         const float* b1, const float* w2, const float* b2, void* out, cudaStream_t stream);
+int launch_split_hilo(const float* x, long long rows, int cols, long long split_row, void* out, cudaStream_t stream);
 int launch_sg_split_hilo(const float* x, long long rows, long long split_row, void* out, cudaStream_t stream);
 int launch_count_below(const float* conf, int n, float thr, int* out, cudaStream_t stream);
 int launch_prune(const float* match, const float* conf, int n0, int n1, float match_thr, float conf_thr, int* pos,

@@ -61,33 +61,39 @@ int launch_sg_kenc_head(const float* kpts, const float* scores, const float* siz
 
 // fp32 rows -> two-term bf16 split for a near-fp32 similarity GEMM on the bf16 tensor cores:
 // x = hi + lo (hi = bf16(x), lo = bf16(x - hi)); rows < split_row (image 0, the A operand) become
-// [hi | hi | lo], the others (image 1, the B operand) [hi | lo | hi], so that one K = 3*256 GEMM
+// [hi | hi | lo], the others (image 1, the B operand) [hi | lo | hi], so that one K = 3 * cols GEMM
 // accumulates hi.hi + hi.lo + lo.hi in fp32 (the dropped lo.lo term is ~2^-16 relative).
-__global__ void __launch_bounds__(256) sg_split_hilo_kernel(const float* __restrict__ x, long long rows,
-                                                            long long split_row, __nv_bfloat16* __restrict__ out) {
+__global__ void __launch_bounds__(256) split_hilo_kernel(const float* __restrict__ x, long long rows, int cols,
+                                                         long long split_row, __nv_bfloat16* __restrict__ out) {
     const long long t = (long long)blockIdx.x * 256 + threadIdx.x;  // one thread per 4 columns
-    if (t >= rows * 64) return;
-    const long long row = t >> 6;
-    const int c = (int)(t & 63) * 4;
-    const float4 v = *reinterpret_cast<const float4*>(x + row * 256 + c);
+    const int per_row = cols >> 2;
+    if (t >= rows * per_row) return;
+    const long long row = t / per_row;
+    const int c = (int)(t - row * per_row) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(x + row * cols + c);
     const __nv_bfloat162 h01 = __floats2bfloat162_rn(v.x, v.y), h23 = __floats2bfloat162_rn(v.z, v.w);
     const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
     const uint32_t lo0 = pack_bf16(v.x - f01.x, v.y - f01.y), lo1 = pack_bf16(v.z - f23.x, v.w - f23.y);
     const uint2 hi = make_uint2(*reinterpret_cast<const uint32_t*>(&h01), *reinterpret_cast<const uint32_t*>(&h23));
     const uint2 lo = make_uint2(lo0, lo1);
-    __nv_bfloat16* o = out + row * 768 + c;
+    __nv_bfloat16* o = out + row * 3 * cols + c;
     const bool a_side = row < split_row;
     *reinterpret_cast<uint2*>(o) = hi;
-    *reinterpret_cast<uint2*>(o + 256) = a_side ? hi : lo;
-    *reinterpret_cast<uint2*>(o + 512) = a_side ? lo : hi;
+    *reinterpret_cast<uint2*>(o + cols) = a_side ? hi : lo;
+    *reinterpret_cast<uint2*>(o + 2 * cols) = a_side ? lo : hi;
+}
+
+int launch_split_hilo(const float* x, long long rows, int cols, long long split_row, void* out, cudaStream_t stream) {
+    B200_REQUIRE(cols > 0 && cols % 4 == 0, "split_hilo: cols=%d must be a positive multiple of 4", cols);
+    if (rows == 0) return 0;
+    split_hilo_kernel<<<(unsigned)((rows * (cols / 4) + 255) / 256), 256, 0, stream>>>(
+        x, rows, cols, split_row, reinterpret_cast<__nv_bfloat16*>(out));
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
 }
 
 int launch_sg_split_hilo(const float* x, long long rows, long long split_row, void* out, cudaStream_t stream) {
-    if (rows == 0) return 0;
-    sg_split_hilo_kernel<<<(unsigned)((rows * 64 + 255) / 256), 256, 0, stream>>>(x, rows, split_row,
-                                                                                reinterpret_cast<__nv_bfloat16*>(out));
-    B200_CHECK_CUDA(cudaGetLastError());
-    return 0;
+    return launch_split_hilo(x, rows, 256, split_row, out, stream);
 }
 
 }  // namespace b200

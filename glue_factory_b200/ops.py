@@ -293,6 +293,31 @@ def sg_split_hilo(x32, rows, split_row, out):
         _lib.check(_lib.lib().b200_sg_split_hilo(_ptr(x32), int(rows), int(split_row), _ptr(out), _stream()))
 
 
+def split_hilo(x32, rows, cols, split_row, out):
+    _require_cuda(x32, out)
+    with _timed("split_hilo", 1, rows * cols * 10.0):
+        _lib.check(_lib.lib().b200_split_hilo(_ptr(x32), int(rows), int(cols), int(split_row), _ptr(out), _stream()))
+
+
+def nn_match(sim, ratio_thresh, distance_thresh, mutual_check):
+    """find_nn both ways + mutual check + log_assignment: (log_assignment [B,M+1,N+1], m0, m1, ms0, ms1)."""
+    _require_cuda(sim)
+    b, m, n = sim.shape
+    dev = sim.device
+    ws = torch.empty(_lib.lib().b200_nn_match_workspace(b, m, n), dtype=torch.uint8, device=dev)
+    la = torch.empty(b, m + 1, n + 1, dtype=torch.float32, device=dev)
+    m0 = torch.empty(b, m, dtype=torch.int64, device=dev)
+    m1 = torch.empty(b, n, dtype=torch.int64, device=dev)
+    ms0 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    ms1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    ratio_sq = float(ratio_thresh) ** 2 if ratio_thresh else 0.0
+    dist_sq = float(distance_thresh) ** 2 if distance_thresh else 0.0
+    with _timed("nn_match", 4, 12.0 * b * m * n):
+        _lib.check(_lib.lib().b200_nn_match(_ptr(sim), b, m, n, ratio_sq, dist_sq, int(bool(mutual_check)), _ptr(ws),
+                                            _ptr(la), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _stream()))
+    return la, m0, m1, ms0, ms1
+
+
 def sg_sinkhorn_assignment(cost, bin_score, iters, threshold):
     """log_optimal_transport + mutual-NN filter: (scores [B,M+1,N+1], m0, m1, ms0, ms1)."""
     _require_cuda(cost, bin_score)

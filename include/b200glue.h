@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 4
+#define B200_ABI_VERSION 5
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -165,6 +165,21 @@ int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, 
                        int B, int M, int N, float filter_threshold, void* workspace,
                        float* scores /*[B,M+1,N+1]*/, long long* matches0, long long* matches1,
                        float* mscores0, float* mscores1, b200_stream_t stream);
+
+
+/* ---- nearest-neighbour matcher (gluefactory/models/matchers/nearest_neighbor_matcher.py) ------ */
+/* fp32 [rows,cols] -> bf16 [rows,3*cols] two-term split feeding a K = 3*cols similarity GEMM with near-fp32
+ * accuracy (the einsum at :52): rows < split_row: [hi|hi|lo] (A side), the others: [hi|lo|hi] (B side). */
+int b200_split_hilo(const float* x, long long rows, int cols, long long split_row, void* out, b200_stream_t stream);
+/* find_nn (:14-25) in both directions, mutual_check (:28-36), matching scores and log_assignment (:59-64) from the
+ * similarity sim [B,M,N]: nearest neighbour by largest similarity (lowest index on ties), squared distance
+ * 2 (1 - sim); the ratio test (d0 <= ratio_thresh_sq * d1) and the distance test (d0 <= distance_thresh_sq) are
+ * disabled when the threshold is <= 0.  log_assignment [B,M+1,N+1] = log_softmax over rows + over columns, last
+ * row / column zero; matches int64, -1 = unmatched; mscores 1.0 for a match, else 0.0. */
+size_t b200_nn_match_workspace(int B, int M, int N);
+int b200_nn_match(const float* sim, int B, int M, int N, float ratio_thresh_sq, float distance_thresh_sq,
+                  int mutual_check, void* workspace, float* log_assignment, long long* matches0, long long* matches1,
+                  float* mscores0, float* mscores1, b200_stream_t stream);
 
 
 /* ---- SuperGlue configuration (gluefactory_nonfree/superglue.py) ------------------------------- */
