@@ -1,3 +1,4 @@
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o scripts/microbench/mufu scripts/microbench/mufu.cu
 // MUFU throughput probe: ex2.approx f32 vs packed f16x2 / bf16x2 (elements per clock per SM)
 #include <cstdio>
 #include <cstdint>
