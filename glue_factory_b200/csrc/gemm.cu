@@ -92,12 +92,27 @@ struct EpiSmem {
 // Row-major outputs go through a per-warp staging tile so that global loads / stores are coalesced:
 // phase A: thread <-> accumulator row (per-column math), phase B: 8 lanes <-> one 128-byte row segment.
 // ---------------------------------------------------------------------------------------------
+// explicit shared-space accesses: through the generic pointers of EpiSmem the compiler emits generic LD.E / ST.E
+// (long-scoreboard latency) and, not knowing that the staging tile and the operands do not alias, serialises
+// every load behind the previous store.  The loads below are issued in batches ahead of their consumers.
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
 template <int BLOCK_N, int EPI>
 __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem& es, uint32_t acc_taddr, int batch,
                                               long long tile_row0, int half, int n0, int lane) {
     uint32_t r[32];
     const bool has_bias = p.bias != nullptr;
     const long long row_base = (long long)batch * p.M;
+    const uint32_t stage = smem_u32(es.stage);
+    const uint32_t bias_s = smem_u32(es.bias);
+    const int cj = lane & 7, rsub = lane >> 3;
     // residual / rotary operands of one 32-column chunk: 8 row groups x 16 B per lane.  They are requested one
     // chunk ahead (while the previous chunk is converted and stored), so their L2 / HBM latency is off the
     // per-chunk critical path; out32 may alias resid, but only within the same chunk (same columns), and
@@ -107,8 +122,8 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
         const int col0 = n0 + c * 32;
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
-            const long long row_in_batch = tile_row0 + it * 4 + (lane >> 3);
-            const int col = col0 + (lane & 7) * 4;
+            const long long row_in_batch = tile_row0 + it * 4 + rsub;
+            const int col = col0 + cj * 4;
             dst[it] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (c < BLOCK_N / 32 && col0 < p.N && row_in_batch < p.M) {
                 const long long grow = row_base + row_in_batch;
@@ -124,33 +139,37 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
     for (int c = half; c < BLOCK_N / 32; c += 2) {
         const int col0 = n0 + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
+        // phase A: thread <-> accumulator row; raw accumulators into the swizzled staging tile
         tmem_ld32(acc_taddr + c * 32, r);
         tmem_ld_wait();
-        uint8_t* myrow = es.stage + lane * 128;
+        const uint32_t myrow = stage + lane * 128;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            float4 v = make_float4(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1]),
-                                   __uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3]));
+        for (int q = 0; q < 8; ++q)
+            sts128(myrow + ((q ^ (lane & 7)) << 4), r[q * 4], r[q * 4 + 1], r[q * 4 + 2], r[q * 4 + 3]);
+        __syncwarp();
+        // phase B: 8 lanes <-> one 128-byte row segment; every staging load is in flight before the first use
+        float4 v8[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            v8[it] = lds128(stage + rr * 128 + ((cj ^ (rr & 7)) << 4));
+        }
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (has_bias) bv = lds128(bias_s + (col0 + cj * 4) * 4);
+        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(c + 2, aux_next);  // next chunk of this warp
+        const int col = col0 + cj * 4;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            float4 v = v8[it];
             if (EPI == EPI_F32) { v.x *= p.alpha; v.y *= p.alpha; v.z *= p.alpha; v.w *= p.alpha; }
-            if (has_bias) {
-                const float4 b = *reinterpret_cast<const float4*>(es.bias + col0 + q * 4);
-                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-            }
+            v.x += bv.x; v.y += bv.y; v.z += bv.z; v.w += bv.w;
             if (EPI == EPI_BIAS_BF16 && p.relu) {
                 v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
             }
-            *reinterpret_cast<float4*>(myrow + ((q ^ (lane & 7)) << 4)) = v;
-        }
-        __syncwarp();
-        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(c + 2, aux_next);  // next chunk of this warp
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-            const int rr = it * 4 + (lane >> 3), cj = lane & 7;
-            float4 v = *reinterpret_cast<const float4*>(es.stage + rr * 128 + ((cj ^ (rr & 7)) << 4));
             const long long row_in_batch = tile_row0 + rr;
             if (row_in_batch >= p.M) continue;
             const long long grow = row_base + row_in_batch;
-            const int col = col0 + cj * 4;
             if constexpr (EPI == EPI_QKV_ROTARY) {
                 if (col0 < p.rot_cols) {
                     // (cos, sin) of frequencies (col & 63) / 2 and + 1
@@ -448,8 +467,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 mbar_wait(empty_bar + stage, phase ^ 1);
                 uint8_t* sa = smem + stage * Cfg::kStageBytes;
                 uint8_t* sb = sa + Cfg::kABytes;
+                const bool dbg_skip_b = (p.dbg & 2) && t != blockIdx.x;
                 if (leader) {
-                    mbar_arrive_expect_tx(full_bar + stage, Cfg::kStageBytes);
+                    mbar_arrive_expect_tx(full_bar + stage, dbg_skip_b ? Cfg::kABytes : Cfg::kStageBytes);
                     if constexpr (A_MODE == 0) {
                         tma_load_2d(sa, &tmap_a, full_bar + stage, kb * kBlockK, b * p.a_batch_rows + mt * kBlockM);
                     } else {
@@ -461,6 +481,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     }
 #pragma unroll
                     for (int h = 0; h < Cfg::kNumUmmaN; ++h)
+                        if (!dbg_skip_b)
                         tma_load_2d(sb + h * Cfg::kUmmaN * kBlockK * 2, &tmap_b, full_bar + stage, kb * kBlockK,
                                     brow + h * Cfg::kUmmaN);
                 }
@@ -539,6 +560,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const long long rest = t / n_tiles;
             const int mt = (int)(rest % m_tiles);
             const int b = (int)(rest / m_tiles);
+            if (p.dbg & 1) {
+                for (int hh = 0; hh < kHalves; ++hh) {
+                    mbar_wait(acc_full + acc, acc_phase);
+                    tc_fence_after();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_empty + acc);
+                    if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
+                }
+                continue;
+            }
             if constexpr (EPI == EPI_LN_GELU) {
                 // accumulator stage h holds columns [256 h, 256 h + 256) of this row tile; both stages turn over once
                 // per tile, so one phase bit serves both.  `half` is this warp's column group (0..3) here.
