@@ -165,7 +165,6 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
     p.out16 = d->out16; p.ld16 = d->ld16; p.out32 = d->out32; p.ld32 = d->ld32;
     p.out32_batch_stride = d->out32_batch_stride;
     p.cells_h = d->cells_h; p.cells_w = d->cells_w;
-    p.dbg = env_int("B200_GEMM_DBG", 0);
     B200_REQUIRE(d->batch >= 0 && d->N >= 1, "gemm: bad shape (batch=%d, N=%d)", d->batch, d->N);
     if (d->batch == 0) return 0;
 

@@ -467,9 +467,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 mbar_wait(empty_bar + stage, phase ^ 1);
                 uint8_t* sa = smem + stage * Cfg::kStageBytes;
                 uint8_t* sb = sa + Cfg::kABytes;
-                const bool dbg_skip_b = (p.dbg & 2) && t != blockIdx.x;
                 if (leader) {
-                    mbar_arrive_expect_tx(full_bar + stage, dbg_skip_b ? Cfg::kABytes : Cfg::kStageBytes);
+                    mbar_arrive_expect_tx(full_bar + stage, Cfg::kStageBytes);
                     if constexpr (A_MODE == 0) {
                         tma_load_2d(sa, &tmap_a, full_bar + stage, kb * kBlockK, b * p.a_batch_rows + mt * kBlockM);
                     } else {
@@ -481,7 +480,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                     }
 #pragma unroll
                     for (int h = 0; h < Cfg::kNumUmmaN; ++h)
-                        if (!dbg_skip_b)
                         tma_load_2d(sb + h * Cfg::kUmmaN * kBlockK * 2, &tmap_b, full_bar + stage, kb * kBlockK,
                                     brow + h * Cfg::kUmmaN);
                 }
@@ -560,17 +558,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const long long rest = t / n_tiles;
             const int mt = (int)(rest % m_tiles);
             const int b = (int)(rest / m_tiles);
-            if (p.dbg & 1) {
-                for (int hh = 0; hh < kHalves; ++hh) {
-                    mbar_wait(acc_full + acc, acc_phase);
-                    tc_fence_after();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(acc_empty + acc);
-                    if (++acc == Cfg::kAccStages) { acc = 0; acc_phase ^= 1; }
-                }
-                continue;
-            }
             if constexpr (EPI == EPI_LN_GELU) {
                 // accumulator stage h holds columns [256 h, 256 h + 256) of this row tile; both stages turn over once
                 // per tile, so one phase bit serves both.  `half` is this warp's column group (0..3) here.

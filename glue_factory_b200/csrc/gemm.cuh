@@ -41,7 +41,6 @@ struct GemmParams {
     long long ld32;
     long long out32_batch_stride;
     int cells_h, cells_w;  // EPI_CONV_BN_SOFTMAX_D2S: rows are (img, cell_y, cell_x)
-    int dbg;
 };
 
 }  // namespace b200

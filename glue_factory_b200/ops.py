@@ -24,11 +24,15 @@ def _stream():
 class _Stats:
     launches = 0
     profile = None  # None, or a list collecting (tag, work, start_event, end_event)
+    only = None     # None = every launch is bracketed when profiling, else the set of tags to bracket
 
 
-def reset_stats(profile=False):
+def reset_stats(profile=False, only=None):
+    """`only`: bracket just these tags (two event records per launch cost ~1 us of stream time each, which
+    shows in a step of 130 launches; the timed region of bench.py brackets the dominant kernel alone)."""
     _Stats.launches = 0
     _Stats.profile = [] if profile else None
+    _Stats.only = set(only) if only else None
 
 
 def launches():
@@ -47,13 +51,14 @@ class _timed:
 
     def __enter__(self):
         _Stats.launches += self.n
-        if _Stats.profile is not None:
+        self.on = _Stats.profile is not None and (_Stats.only is None or self.tag in _Stats.only)
+        if self.on:
             self.t0 = torch.cuda.Event(enable_timing=True)
             self.t1 = torch.cuda.Event(enable_timing=True)
             self.t0.record()
 
     def __exit__(self, *exc):
-        if _Stats.profile is not None:
+        if self.on:
             self.t1.record()
             _Stats.profile.append((self.tag, self.work, self.t0, self.t1))
         return False
