@@ -216,15 +216,18 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
 __device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_taddr, int col_base, int grp,
                                               float& sum, float& sumsq) {
     uint32_t r[32];
+    const uint32_t bias_s = smem_u32(es.bias);
 #pragma unroll 1
     for (int c = grp; c < 8; c += 4) {
         tmem_ld32(half_taddr + c * 32, r);
+        float4 b[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) b[q] = lds128(bias_s + (col_base + c * 32 + q * 4) * 4);  // under the TMEM load
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-            const float4 b = *reinterpret_cast<const float4*>(es.bias + col_base + c * 32 + q * 4);
-            const float x0 = __uint_as_float(r[q * 4]) + b.x, x1 = __uint_as_float(r[q * 4 + 1]) + b.y;
-            const float x2 = __uint_as_float(r[q * 4 + 2]) + b.z, x3 = __uint_as_float(r[q * 4 + 3]) + b.w;
+            const float x0 = __uint_as_float(r[q * 4]) + b[q].x, x1 = __uint_as_float(r[q * 4 + 1]) + b[q].y;
+            const float x2 = __uint_as_float(r[q * 4 + 2]) + b[q].z, x3 = __uint_as_float(r[q * 4 + 3]) + b[q].w;
             sum += (x0 + x1) + (x2 + x3);
             sumsq = fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, fmaf(x3, x3, sumsq))));
         }
@@ -234,6 +237,8 @@ __device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_t
 __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem& es, uint32_t half_taddr, int col_base,
                                              long long tile_row0, int grp, int lane, float rstd, float nmr) {
     uint32_t r[32];
+    const uint32_t bias_s = smem_u32(es.bias), g_s = smem_u32(es.par1), be_s = smem_u32(es.par2);
+    const uint32_t stage = smem_u32(es.stage);
 #pragma unroll 1
     for (int c = grp; c < 8; c += 4) {
         tmem_ld32(half_taddr + c * 32, r);
@@ -241,10 +246,10 @@ __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem&
         uint32_t pk[16];
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-            const int col = col_base + c * 32 + q * 4;
-            const float4 b = *reinterpret_cast<const float4*>(es.bias + col);
-            const float4 g = *reinterpret_cast<const float4*>(es.par1 + col);
-            const float4 be = *reinterpret_cast<const float4*>(es.par2 + col);
+            const uint32_t off = (col_base + c * 32 + q * 4) * 4;
+            const float4 b = lds128(bias_s + off);
+            const float4 g = lds128(g_s + off);
+            const float4 be = lds128(be_s + off);
             const float y0 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4]) + b.x, rstd, nmr), g.x, be.x));
             const float y1 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 1]) + b.y, rstd, nmr), g.y, be.y));
             const float y2 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 2]) + b.z, rstd, nmr), g.z, be.z));
@@ -253,20 +258,24 @@ __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem&
             pk[q * 2 + 1] = pack_bf16(y2, y3);
         }
         // staging rows are 64 B (32 bf16): 16-byte chunk j of row l sits at l*64 + ((j ^ ((l >> 1) & 3)) << 4)
-        uint8_t* myrow = es.stage + lane * 64;
+        const uint32_t myrow = stage + lane * 64;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<uint4*>(myrow + ((j ^ ((lane >> 1) & 3)) << 4)) =
-                make_uint4(pk[j * 4], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
+            sts128(myrow + ((j ^ ((lane >> 1) & 3)) << 4), pk[j * 4], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
         __syncwarp();
+        float4 v4[4];
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
             const int rr = it * 8 + (lane >> 2), cj = lane & 3;
-            const uint4 v = *reinterpret_cast<const uint4*>(es.stage + rr * 64 + ((cj ^ ((rr >> 1) & 3)) << 4));
+            v4[it] = lds128(stage + rr * 64 + ((cj ^ ((rr >> 1) & 3)) << 4));
+        }
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int rr = it * 8 + (lane >> 2), cj = lane & 3;
             const long long grow = tile_row0 + rr;
             if (grow < p.M)
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col_base + c * 32 +
-                                          cj * 8) = v;
+                *reinterpret_cast<float4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + grow * p.ld16 + col_base + c * 32 +
+                                           cj * 8) = v4[it];
         }
         __syncwarp();
     }
