@@ -40,6 +40,13 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// 1024-byte alignment of the dynamic shared-memory base by pointer arithmetic on the __shared__ array: a round
+// trip through uintptr_t hides the address space from the compiler, which then emits generic LD / ST (long
+// scoreboard) for every shared-memory access derived from the pointer.
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* smem_raw) {
+    return smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+}
+
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred = 0;
     asm volatile(

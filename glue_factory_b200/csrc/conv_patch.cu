@@ -53,7 +53,7 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                   const GemmParams p) {
     using Cfg = ConvPatchCfg<COUT>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = align_smem_1024(smem_raw);
     uint8_t* sW = smem;
     uint8_t* sA = smem + Cfg::kWBytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(sA + Cfg::kStages * kCpPatchBytes);

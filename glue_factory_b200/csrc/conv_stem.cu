@@ -65,7 +65,7 @@ __device__ __forceinline__ void st_split(float v, float& hi, float& lo) {
 __global__ void __launch_bounds__(kStThreads, 1)
 conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = align_smem_1024(smem_raw);
     uint8_t* sW = smem;
     uint8_t* sPatch = sW + kStWBytes;
     uint8_t* sA = sPatch + kStPatchStages * kStPatchBytes;
