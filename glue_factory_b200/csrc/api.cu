@@ -117,6 +117,14 @@ static int make_map_2d(CUtensorMap* out, const void* ptr, long long rows, long l
     return make_map(out, ptr, 2, dims, strides, box);
 }
 
+bool pdl_enabled() {
+    static const bool on = [] {
+        const char* v = getenv("B200_PDL");
+        return v == nullptr || atoi(v) != 0;
+    }();
+    return on;
+}
+
 static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
     return v ? atoi(v) : dflt;

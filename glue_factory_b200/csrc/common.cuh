@@ -34,6 +34,37 @@ void set_last_error(const char* fmt, ...);
     } while (0)
 
 // ---------------------------------------------------------------------------------------------
+// programmatic dependent launch: a kernel launched with launch_pdl() may become resident while its predecessor
+// in the stream is still running; it runs its prologue (barrier init, TMEM allocation, descriptor prefetch),
+// then pdl_wait() blocks until the predecessor grid has completed and its writes are visible.  Every kernel
+// launched this way calls pdl_wait() on all paths before its first global-memory access.  pdl_trigger() lets
+// the successor start becoming resident (it still waits for our completion in its own pdl_wait()).
+// B200_PDL=0 in the environment launches everything fully serialised (A/B measurement).
+// ---------------------------------------------------------------------------------------------
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+
+// ---------------------------------------------------------------------------------------------
 // small device utilities
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

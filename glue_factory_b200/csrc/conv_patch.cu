@@ -90,6 +90,8 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    pdl_wait();     // predecessor grid complete, its writes visible (prologue above overlapped its tail)
+    pdl_trigger();  // successor may become resident
 
     if (warp == 0) {
         if (lane == 0) {
@@ -248,8 +250,7 @@ static int launch_conv_patch_t(const CUtensorMap& ta, const CUtensorMap& tw, con
     const long long total = (long long)p.batch * p.tiles_x * p.tiles_y;
     if (total == 0) return 0;
     const int grid = (int)(total < num_sms ? total : num_sms);
-    kern<<<grid, kCpThreads, Cfg::kSmemBytes, stream>>>(ta, tw, p);
-    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kCpThreads), Cfg::kSmemBytes, stream, ta, tw, p));
     return 0;
 }
 

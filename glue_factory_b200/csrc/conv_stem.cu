@@ -104,6 +104,8 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    pdl_wait();     // predecessor grid complete, its writes visible (prologue above overlapped its tail)
+    pdl_trigger();  // successor may become resident
 
     if (warp == 0) {
         if (elect_one()) {
@@ -420,8 +422,7 @@ int launch_conv_stem(const CUtensorMap& tw, const StemParams& p, int num_sms, cu
     if (total == 0) return 0;
     B200_REQUIRE(total < (1ll << 31), "conv_stem: too many tiles");
     const int grid = (int)(total < num_sms ? total : num_sms);
-    conv_stem_kernel<<<grid, kStThreads, kStSmemBytes, stream>>>(tw, p);
-    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(launch_pdl(conv_stem_kernel, dim3(grid), dim3(kStThreads), kStSmemBytes, stream, tw, p));
     return 0;
 }
 

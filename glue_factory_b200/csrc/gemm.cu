@@ -458,6 +458,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    pdl_wait();     // predecessor grid complete, its writes visible (prologue above overlapped its tail)
+    pdl_trigger();  // successor may become resident
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -653,8 +655,7 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
     const long long total = (long long)p.batch * m_tiles * n_tiles;
     if (total == 0) return 0;
     const int grid = (int)(total < num_sms ? total : num_sms);
-    kern<<<grid, gemm_threads(EPI), Cfg::kSmemBytes, stream>>>(ta, tb, p);
-    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(gemm_threads(EPI)), Cfg::kSmemBytes, stream, ta, tb, p));
     return 0;
 }
 
