@@ -19,8 +19,17 @@
 
 namespace b200 {
 
-constexpr int kEW = 128, kEH = 96, kSeg = 16;
-constexpr int kNmsFastThreads = 512;
+#ifndef NMS_EH
+#define NMS_EH 96
+#endif
+#ifndef NMS_MINB
+#define NMS_MINB 2
+#endif
+constexpr int kEW = 128, kEH = NMS_EH, kSeg = 16;
+#ifndef NMS_THREADS
+#define NMS_THREADS 512
+#endif
+constexpr int kNmsFastThreads = NMS_THREADS;
 constexpr int kMaskWords = 6;  // [guard | 4 words = 128 columns | guard]
 
 __device__ __forceinline__ uint32_t order_key32(float v) {
@@ -143,7 +152,7 @@ __device__ __forceinline__ void dilate(const uint32_t* __restrict__ mask, uint32
 }
 
 template <int R>
-__global__ void __launch_bounds__(kNmsFastThreads, 2)
+__global__ void __launch_bounds__(kNmsFastThreads, NMS_MINB)
 nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const int* __restrict__ image_hw,
                 float* __restrict__ out, unsigned long long* __restrict__ cand, int* __restrict__ cand_count, int cap) {
     using G = NmsGeom<R>;
