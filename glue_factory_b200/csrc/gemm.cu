@@ -106,7 +106,8 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 
 template <int BLOCK_N, int EPI>
 __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem& es, uint32_t acc_taddr, int batch,
-                                              long long tile_row0, int half, int n0, int lane) {
+                                              long long tile_row0, int half, int n0, int lane, uint64_t* acc_full_bar,
+                                              uint32_t acc_full_phase) {
     uint32_t r[32];
     const bool has_bias = p.bias != nullptr;
     const long long row_base = (long long)batch * p.M;
@@ -134,7 +135,12 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
             }
         }
     };
+    // first operands are requested before the accumulator is awaited.  Rotary: a warp's chunks (half, half + 2, ...)
+    // all cover the same 16 frequencies of the same rows (64-column heads, 256-column tiles), so the (cos, sin)
+    // slice is loaded once per tile, not per chunk.
     if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(half, aux);
+    mbar_wait(acc_full_bar, acc_full_phase);
+    tc_fence_after();
 #pragma unroll 1
     for (int c = half; c < BLOCK_N / 32; c += 2) {
         const int col0 = n0 + c * 32;
@@ -156,7 +162,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
         }
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
         if (has_bias) bv = lds128(bias_s + (col0 + cj * 4) * 4);
-        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(c + 2, aux_next);  // next chunk of this warp
+        if constexpr (EPI == EPI_RESID) load_aux(c + 2, aux_next);  // next chunk of this warp
         const int col = col0 + cj * 4;
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
@@ -201,7 +207,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
                 *reinterpret_cast<uint2*>(o16) = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
             }
         }
-        if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) {
+        if constexpr (EPI == EPI_RESID) {
 #pragma unroll
             for (int it = 0; it < 8; ++it) aux[it] = aux_next[it];
         }
@@ -606,12 +612,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 acc_phase ^= 1;
                 continue;
             }
-            mbar_wait(acc_full + acc, acc_phase);
-            tc_fence_after();
             const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + ((uint32_t)(quarter * 32) << 16);
             if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_QKV_ROTARY || EPI == EPI_RESID || EPI == EPI_F32) {
-                epilogue_rows<BLOCK_N, EPI>(p, es, taddr, b, (long long)mt * kBlockM + quarter * 32, half, nt * BLOCK_N, lane);
+                epilogue_rows<BLOCK_N, EPI>(p, es, taddr, b, (long long)mt * kBlockM + quarter * 32, half, nt * BLOCK_N, lane,
+                                            acc_full + acc, acc_phase);
             } else {
+                mbar_wait(acc_full + acc, acc_phase);
+                tc_fence_after();
                 long long row_in_batch = 0;
                 bool row_valid;
                 int py = 0, px = 0;
