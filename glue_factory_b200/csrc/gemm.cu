@@ -70,6 +70,55 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return fmaf(fabsf(hx), fmaf(-poly, e, 1.0f), hx);
 }
 
+// packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2 on sm_100: two fp32 operations per issue slot).  A pair lives in
+// an aligned 64-bit register pair; consecutive tcgen05.ld results and float4 halves already are such pairs.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 bc2(float a) { return pk2(a, a); }
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// gelu_erf on two elements at once: 12 packed FMA-pipe instructions + 2 LOP + 4 MUFU per pair
+__device__ __forceinline__ f32x2 gelu_erf2(f32x2 x) {
+    float x0, x1;
+    upk2(x, x0, x1);
+    const f32x2 ax = pk2(fabsf(x0), fabsf(x1));
+    float d0, d1, a0, a1, t0, t1, e0, e1;
+    upk2(fma2(ax, bc2(0.23164189f), bc2(1.0f)), d0, d1);
+    upk2(mul2(mul2(x, bc2(-0.72134752f)), x), a0, a1);
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+    const f32x2 t = pk2(t0, t1), e = pk2(e0, e1);
+    // -poly(t): the coefficients carry the sign, so that 1 - poly e is one FMA
+    f32x2 np = fma2(t, bc2(-1.061405429f), bc2(1.453152027f));
+    np = fma2(t, np, bc2(-1.421413741f));
+    np = fma2(t, np, bc2(0.284496736f));
+    np = fma2(t, np, bc2(-0.254829592f));
+    np = mul2(np, t);
+    const f32x2 w = fma2(np, e, bc2(1.0f));
+    return fma2(mul2(ax, bc2(0.5f)), w, mul2(x, bc2(0.5f)));
+}
+
 __device__ __forceinline__ void store16B(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     *reinterpret_cast<uint4*>(p) = make_uint4(a, b, c, d);
 }
@@ -223,6 +272,7 @@ __device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_t
                                               float& sum, float& sumsq) {
     uint32_t r[32];
     const uint32_t bias_s = smem_u32(es.bias);
+    f32x2 sum2 = bc2(0.f), sq2 = bc2(0.f);
 #pragma unroll 1
     for (int c = grp; c < 8; c += 4) {
         tmem_ld32(half_taddr + c * 32, r);
@@ -232,12 +282,17 @@ __device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_t
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-            const float x0 = __uint_as_float(r[q * 4]) + b[q].x, x1 = __uint_as_float(r[q * 4 + 1]) + b[q].y;
-            const float x2 = __uint_as_float(r[q * 4 + 2]) + b[q].z, x3 = __uint_as_float(r[q * 4 + 3]) + b[q].w;
-            sum += (x0 + x1) + (x2 + x3);
-            sumsq = fmaf(x0, x0, fmaf(x1, x1, fmaf(x2, x2, fmaf(x3, x3, sumsq))));
+            const f32x2 xa = add2(pk2(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1])), pk2(b[q].x, b[q].y));
+            const f32x2 xb = add2(pk2(__uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])), pk2(b[q].z, b[q].w));
+            sum2 = add2(sum2, add2(xa, xb));
+            sq2 = fma2(xa, xa, fma2(xb, xb, sq2));
         }
     }
+    float s0, s1, q0, q1;
+    upk2(sum2, s0, s1);
+    upk2(sq2, q0, q1);
+    sum += s0 + s1;
+    sumsq += q0 + q1;
 }
 
 __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem& es, uint32_t half_taddr, int col_base,
@@ -245,6 +300,7 @@ __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem&
     uint32_t r[32];
     const uint32_t bias_s = smem_u32(es.bias), g_s = smem_u32(es.par1), be_s = smem_u32(es.par2);
     const uint32_t stage = smem_u32(es.stage);
+    const f32x2 rstd2 = bc2(rstd), nmr2 = bc2(nmr);
 #pragma unroll 1
     for (int c = grp; c < 8; c += 4) {
         tmem_ld32(half_taddr + c * 32, r);
@@ -256,10 +312,13 @@ __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem&
             const float4 b = lds128(bias_s + off);
             const float4 g = lds128(g_s + off);
             const float4 be = lds128(be_s + off);
-            const float y0 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4]) + b.x, rstd, nmr), g.x, be.x));
-            const float y1 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 1]) + b.y, rstd, nmr), g.y, be.y));
-            const float y2 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 2]) + b.z, rstd, nmr), g.z, be.z));
-            const float y3 = gelu_erf(fmaf(fmaf(__uint_as_float(r[q * 4 + 3]) + b.w, rstd, nmr), g.w, be.w));
+            const f32x2 xa = add2(pk2(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1])), pk2(b.x, b.y));
+            const f32x2 xb = add2(pk2(__uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])), pk2(b.z, b.w));
+            const f32x2 ya = gelu_erf2(fma2(fma2(xa, rstd2, nmr2), pk2(g.x, g.y), pk2(be.x, be.y)));
+            const f32x2 yb = gelu_erf2(fma2(fma2(xb, rstd2, nmr2), pk2(g.z, g.w), pk2(be.z, be.w)));
+            float y0, y1, y2, y3;
+            upk2(ya, y0, y1);
+            upk2(yb, y2, y3);
             pk[q * 2] = pack_bf16(y0, y1);
             pk[q * 2 + 1] = pack_bf16(y2, y3);
         }
