@@ -55,21 +55,48 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
-// 2^x on the FMA pipe (Cody-Waite: round to nearest integer through the 1.5 * 2^23 trick, degree-3 polynomial
-// on [-0.5, 0.5], exponent added as an integer): relative error <= 7.5e-5, far below the bf16 rounding of P.
-// The exponentials bound this kernel on the 16-lane MUFU; a fraction of them (ATT_POLY_PER_64 of every 64) takes
-// this path so that MUFU and issue slots are both kept busy.
-#ifndef ATT_POLY_PER_64
-#define ATT_POLY_PER_64 4
+// packed fp32x2 arithmetic (FFMA2 / FADD2 on sm_100): two fp32 operations per issue slot
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 bc2(float a) { return pk2(a, a); }
+__device__ __forceinline__ void upk2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// 2^x on the FMA pipe for a pair of elements (Cody-Waite: round to nearest integer through the 1.5 * 2^23 trick,
+// degree-3 polynomial on [-0.5, 0.5], exponent added as an integer): relative error <= 7.5e-5, far below the bf16
+// rounding of P.  The exponentials bound this kernel on the 16-lane MUFU; ATT_POLY_PAIRS of the 32 key pairs of a
+// tile row take this path (packed: 2 FMNMX + 6 FFMA2 / FADD2 + 2 shift-adds per pair) so that MUFU and issue
+// slots are both kept busy.
+#ifndef ATT_POLY_PAIRS
+#define ATT_POLY_PAIRS 4
 #endif
-__device__ __forceinline__ float ex2_poly(float x) {
-    x = fmaxf(x, -125.0f);
-    const float t = x + 12582912.0f;
-    const float f = x - (t - 12582912.0f);
-    float q = fmaf(f, 0.05517173558473587f, 0.2426111251115799f);
-    q = fmaf(q, f, 0.6932609677314758f);
-    q = fmaf(q, f, 0.9999280571937561f);
-    return __int_as_float(__float_as_int(q) + (__float_as_int(t) << 23));
+__device__ __forceinline__ void ex2_poly2(f32x2 x, float& e0, float& e1) {
+    float x0, x1;
+    upk2(x, x0, x1);
+    x = pk2(fmaxf(x0, -125.0f), fmaxf(x1, -125.0f));
+    const f32x2 t = add2(x, bc2(12582912.0f));
+    const f32x2 f = fma2(add2(t, bc2(-12582912.0f)), bc2(-1.0f), x);
+    f32x2 q = fma2(f, bc2(0.05517173558473587f), bc2(0.2426111251115799f));
+    q = fma2(q, f, bc2(0.6932609677314758f));
+    q = fma2(q, f, bc2(0.9999280571937561f));
+    float q0, q1, t0, t1;
+    upk2(q, q0, q1);
+    upk2(t, t0, t1);
+    e0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+    e1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
 }
 
 // one work item, decoded identically by every warp (all fields warp-uniform)
@@ -301,18 +328,27 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                         tmem_st8(tmem_o + ch * 8, t8);
                     }
                 }
-                const float mc = m_run * c;
-                float l0 = 0.f, l1 = 0.f;
+                const f32x2 c2 = bc2(c), nmc2 = bc2(-m_run * c);
+                f32x2 l2 = bc2(0.f);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {  // column i of the P row = keys (2i, 2i+1) as bf16
-                    constexpr int kPolyStride = ATT_POLY_PER_64 > 0 ? 32 / ATT_POLY_PER_64 : 64;
-                    const bool poly = ATT_POLY_PER_64 > 0 && (i % kPolyStride) == kPolyStride - 1;
-                    const float e0 = ex2_approx(fmaf(sv[2 * i], c, -mc));
-                    const float e1 = poly ? ex2_poly(fmaf(sv[2 * i + 1], c, -mc)) : ex2_approx(fmaf(sv[2 * i + 1], c, -mc));
-                    l0 += e0;
-                    l1 += e1;
+                    constexpr int kPolyStride = ATT_POLY_PAIRS > 0 ? 32 / ATT_POLY_PAIRS : 64;
+                    const bool poly = ATT_POLY_PAIRS > 0 && (i % kPolyStride) == kPolyStride - 1;
+                    const f32x2 a = fma2(pk2(sv[2 * i], sv[2 * i + 1]), c2, nmc2);
+                    float e0, e1;
+                    if (poly) {
+                        ex2_poly2(a, e0, e1);
+                    } else {
+                        float a0, a1;
+                        upk2(a, a0, a1);
+                        e0 = ex2_approx(a0);
+                        e1 = ex2_approx(a1);
+                    }
+                    l2 = add2(l2, pk2(e0, e1));
                     r[i] = pack_bf16(e0, e1);
                 }
+                float l0, l1;
+                upk2(l2, l0, l1);
                 tmem_st32(tmem_s, r);  // P over the first half of S (this thread's own row)
                 tmem_st_wait();
                 l_run += l0 + l1;
