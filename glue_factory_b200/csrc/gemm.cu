@@ -190,6 +190,57 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
     if constexpr (EPI == EPI_RESID || EPI == EPI_QKV_ROTARY) load_aux(half, aux);
     mbar_wait(acc_full_bar, acc_full_phase);
     tc_fence_after();
+    if constexpr (EPI == EPI_BIAS_BF16) {
+        // bf16 output with per-column operands only: bias (+ ReLU) and the bf16 rounding happen in the thread <-> row
+        // phase (packed fp32x2 adds, bias by broadcast loads under the TMEM load), so the staging tile holds 64-byte bf16
+        // rows - half the staging traffic and half the load / store instructions of the fp32 path below.  The two 2 KB
+        // halves of the warp's staging area alternate, which saves the second warp barrier of a chunk.
+        const int cj4 = lane & 3, rsub8 = lane >> 2;
+        int buf = 0;
+#pragma unroll 1
+        for (int c = half; c < BLOCK_N / 32; c += 2, buf ^= 1) {
+            const int col0 = n0 + c * 32;
+            if (col0 >= p.N) break;  // warp-uniform
+            tmem_ld32(acc_taddr + c * 32, r);
+            float4 b[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                b[q] = has_bias ? lds128(bias_s + (col0 + q * 4) * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                float y0, y1, y2, y3;
+                upk2(add2(pk2(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1])), pk2(b[q].x, b[q].y)), y0, y1);
+                upk2(add2(pk2(__uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])), pk2(b[q].z, b[q].w)), y2, y3);
+                if (p.relu) { y0 = fmaxf(y0, 0.f); y1 = fmaxf(y1, 0.f); y2 = fmaxf(y2, 0.f); y3 = fmaxf(y3, 0.f); }
+                pk[q * 2] = pack_bf16(y0, y1);
+                pk[q * 2 + 1] = pack_bf16(y2, y3);
+            }
+            // 64-byte rows: 16-byte chunk j of row l sits at l*64 + ((j ^ ((l >> 1) & 3)) << 4)
+            const uint32_t st = stage + buf * 2048;
+            const uint32_t myrow = st + lane * 64;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                sts128(myrow + ((j ^ ((lane >> 1) & 3)) << 4), pk[j * 4], pk[j * 4 + 1], pk[j * 4 + 2], pk[j * 4 + 3]);
+            __syncwarp();
+            float4 v4[4];
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+                const int rr = it * 8 + rsub8;
+                v4[it] = lds128(st + rr * 64 + ((cj4 ^ ((rr >> 1) & 3)) << 4));
+            }
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+                const long long row_in_batch = tile_row0 + it * 8 + rsub8;
+                if (row_in_batch < p.M)
+                    *reinterpret_cast<float4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + (row_base + row_in_batch) * p.ld16 +
+                                               col0 + cj4 * 8) = v4[it];
+            }
+        }
+        __syncwarp();
+        return;
+    }
 #pragma unroll 1
     for (int c = half; c < BLOCK_N / 32; c += 2) {
         const int col0 = n0 + c * 32;
