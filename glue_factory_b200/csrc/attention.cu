@@ -83,6 +83,9 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 #ifndef ATT_POLY_PAIRS
 #define ATT_POLY_PAIRS 4
 #endif
+#ifndef ATT_P_STORE8
+#define ATT_P_STORE8 1
+#endif
 __device__ __forceinline__ void ex2_poly2(f32x2 x, float& e0, float& e1) {
     float x0, x1;
     upk2(x, x0, x1);
@@ -330,6 +333,9 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 }
                 const f32x2 c2 = bc2(c), nmc2 = bc2(-m_run * c);
                 f32x2 l2 = bc2(0.f);
+#if ATT_P_STORE8
+                uint32_t r8[8];
+#endif
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {  // column i of the P row = keys (2i, 2i+1) as bf16
                     constexpr int kPolyStride = ATT_POLY_PAIRS > 0 ? 32 / ATT_POLY_PAIRS : 64;
@@ -345,11 +351,20 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                         e1 = ex2_approx(a1);
                     }
                     l2 = add2(l2, pk2(e0, e1));
+#if ATT_P_STORE8
+                    // P goes back to TMEM eight columns at a time: a 32-register store block next to the 64 S registers
+                    // does not fit the 96 registers of a 544-thread CTA without spills
+                    r8[i & 7] = pack_bf16(e0, e1);
+                    if ((i & 7) == 7) tmem_st8(tmem_s + (i & ~7), r8);
+#else
                     r[i] = pack_bf16(e0, e1);
+#endif
                 }
                 float l0, l1;
                 upk2(l2, l0, l1);
+#if !ATT_P_STORE8
                 tmem_st32(tmem_s, r);  // P over the first half of S (this thread's own row)
+#endif
                 tmem_st_wait();
                 l_run += l0 + l1;
                 tc_fence_before();
