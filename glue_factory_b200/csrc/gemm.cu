@@ -30,23 +30,29 @@ constexpr int kEpiWarpsLn = 16;
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == EPI_LN_GELU ? kEpiWarpsLn : kEpiWarps; }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged in smem (bias | scale/gamma | shift/beta)
-constexpr int kStageBytesPerWarp = 4096;  // 32 rows x 128 B staging per epilogue warp
-constexpr int kStageBytesPerWarpLn = 2048;  // 32 rows x 64 B in the LayerNorm + GELU epilogue
-static_assert(kEpiWarps * kStageBytesPerWarp == kEpiWarpsLn * kStageBytesPerWarpLn, "one staging area for both layouts");
-constexpr int kEpiSmemBytes = kParamFloats * 4 + kEpiWarps * kStageBytesPerWarp + 2 * 128 * 4 * 8;
+// staging per epilogue warp: 32 rows x 128 B (fp32 row epilogues) or 32 rows x 64 B (bf16 rows: plain bf16 and
+// LayerNorm + GELU epilogues); the LayerNorm epilogue adds the per-row statistics exchange
+__host__ __device__ constexpr int stage_bytes_per_warp(int epi) { return (epi == EPI_LN_GELU || epi == EPI_BIAS_BF16) ? 2048 : 4096; }
+__host__ __device__ constexpr int epi_smem_bytes(int epi) {
+    return kParamFloats * 4 + epi_warps(epi) * stage_bytes_per_warp(epi) + (epi == EPI_LN_GELU ? 2 * 128 * 4 * 8 : 0);
+}
 
-template <int BLOCK_N>
+template <int BLOCK_N, int EPI>
 struct GemmCfg {
     static constexpr int kABytes = kBlockM * kBlockK * 2;
     static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (176 * 1024 / kStageBytes) > 8 ? 8 : (176 * 1024 / kStageBytes);
+    // the ring takes what the epilogue leaves: four 48 KB stages for the plain bf16 epilogue at 256 columns (one whole
+    // K = 256 tile in flight), three for the fp32-staged ones
+    static constexpr int kRingBudget = 227 * 1024 - 1024 - 256 - epi_smem_bytes(EPI);
+    static constexpr int kStages = (kRingBudget / kStageBytes) > 8 ? 8 : (kRingBudget / kStageBytes);
     static constexpr int kAccStages = BLOCK_N <= 256 ? 2 : 1;
     static constexpr int kAccStride = BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : (BLOCK_N <= 256 ? 256 : 512));
     static constexpr int kTmemCols = kAccStride * kAccStages < 32 ? 32 : kAccStride * kAccStages;
     static constexpr int kUmmaN = BLOCK_N > 256 ? 256 : BLOCK_N;
     static constexpr int kNumUmmaN = BLOCK_N / kUmmaN;
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiSmemBytes;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + epi_smem_bytes(EPI);
+    static_assert((2 * kStages + 2 * 2) * 8 + 8 <= 256, "barrier block");
     static_assert(kStageBytes % 1024 == 0, "stage must keep 1024-byte alignment for SWIZZLE_128B");
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
@@ -193,12 +199,11 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
     if constexpr (EPI == EPI_BIAS_BF16) {
         // bf16 output with per-column operands only: bias (+ ReLU) and the bf16 rounding happen in the thread <-> row
         // phase (packed fp32x2 adds, bias by broadcast loads under the TMEM load), so the staging tile holds 64-byte bf16
-        // rows - half the staging traffic and half the load / store instructions of the fp32 path below.  The two 2 KB
-        // halves of the warp's staging area alternate, which saves the second warp barrier of a chunk.
+        // rows - half the staging traffic and half the load / store instructions of the fp32 path below - and the ring
+        // gets the shared memory this saves.
         const int cj4 = lane & 3, rsub8 = lane >> 2;
-        int buf = 0;
 #pragma unroll 1
-        for (int c = half; c < BLOCK_N / 32; c += 2, buf ^= 1) {
+        for (int c = half; c < BLOCK_N / 32; c += 2) {
             const int col0 = n0 + c * 32;
             if (col0 >= p.N) break;  // warp-uniform
             tmem_ld32(acc_taddr + c * 32, r);
@@ -218,7 +223,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
                 pk[q * 2 + 1] = pack_bf16(y2, y3);
             }
             // 64-byte rows: 16-byte chunk j of row l sits at l*64 + ((j ^ ((l >> 1) & 3)) << 4)
-            const uint32_t st = stage + buf * 2048;
+            const uint32_t st = stage;
             const uint32_t myrow = st + lane * 64;
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -237,8 +242,8 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
                     *reinterpret_cast<float4*>(reinterpret_cast<__nv_bfloat16*>(p.out16) + (row_base + row_in_batch) * p.ld16 +
                                                col0 + cj4 * 8) = v4[it];
             }
+            __syncwarp();
         }
-        __syncwarp();
         return;
     }
 #pragma unroll 1
@@ -533,7 +538,7 @@ template <int BLOCK_N, int EPI, int A_MODE>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmParams p) {
-    using Cfg = GemmCfg<BLOCK_N>;
+    using Cfg = GemmCfg<BLOCK_N, EPI>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align_smem_1024(smem_raw);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
@@ -543,7 +548,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + Cfg::kAccStages);
     float* s_par = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
     uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_par + kParamFloats);
-    float2* s_exch = reinterpret_cast<float2*>(s_stage + kEpiWarps * kStageBytesPerWarp);
+    float2* s_exch = reinterpret_cast<float2*>(s_stage + epi_warps(EPI) * stage_bytes_per_warp(EPI));  // LayerNorm only
 
     // warp index / TMEM base through a shuffle: the compiler then keeps every UMMA operand in uniform registers
     // (per-lane operands cost an ELECT / R2UR loop of ~75 clk around each tcgen05.mma)
@@ -675,7 +680,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         es.bias = s_par;
         es.par1 = s_par + 768;
         es.par2 = s_par + 1536;
-        es.stage = s_stage + (warp - 2) * (EPI == EPI_LN_GELU ? kStageBytesPerWarpLn : kStageBytesPerWarp);
+        es.stage = s_stage + (warp - 2) * stage_bytes_per_warp(EPI);
         es.exch = s_exch;
         const int r_in_tile = quarter * 32 + lane;
         int acc = 0;
@@ -760,7 +765,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 template <int BLOCK_N, int EPI, int A_MODE>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int num_sms,
                       cudaStream_t stream) {
-    using Cfg = GemmCfg<BLOCK_N>;
+    using Cfg = GemmCfg<BLOCK_N, EPI>;
     auto kern = gemm_tcgen05_kernel<BLOCK_N, EPI, A_MODE>;
     static bool configured = false;
     if (!configured) {
