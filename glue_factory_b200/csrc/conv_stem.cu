@@ -72,7 +72,11 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     uint8_t* sW1 = sA + kStABytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sW1 + kStW1Bytes);
     uint64_t* w_full = bars;            // second-convolution weights landed
-    uint64_t* a_full = bars + 1;        // im2col rows (and, the first time, the stem weight tile) written
+    // [2] im2col rows (and, the first time, the stem weight tile) written, one barrier per tile parity: with a single
+    // barrier the builders could complete two phases (tiles i+1 and i+2) while the issuer was held up on acc_empty by a
+    // slow epilogue, the issuer's parity wait then never returned and the builders waited for its stem GEMM - a
+    // timing-dependent deadlock (seen as a hang under ncu's instrumented replay passes)
+    uint64_t* a_full = bars + 13;
     uint64_t* c1_full = bars + 2;       // [2] stem GEMM retired (even / odd tiles)
     uint64_t* patch_full = bars + 4;    // [2] halo patch written
     uint64_t* patch_empty = bars + 6;   // [2] the 36 MMAs reading it retired
@@ -90,6 +94,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         prefetch_tensormap(&tmap_w);
         mbar_init(w_full, 1);
         mbar_init(a_full, 4);
+        mbar_init(a_full + 1, 4);
         for (int s = 0; s < 2; ++s) {
             mbar_init(c1_full + s, 1);
             mbar_init(patch_full + s, 8);
@@ -145,7 +150,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
             const int st = i & 1;
             if (t + gridDim.x < total_tiles) {  // stem GEMM of the next tile first: its workers are waiting
-                mbar_wait(a_full, (uint32_t)((i + 1) & 1));
+                mbar_wait(a_full + ((i + 1) & 1), (uint32_t)(((i + 1) >> 1) & 1));
                 tc_fence_after();
                 issue_stem((i + 1) & 1);
             }
@@ -343,7 +348,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             }
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(a_full);
+            if (lane == 0) mbar_arrive(a_full + par);
         };
         float nxt0 = 0.f, nxt1 = 0.f;
         if (builder && blockIdx.x < total_tiles) {
