@@ -4,7 +4,6 @@
 mkdir -p gpurun_out
 TAG="${1:-r01}"; shift
 WHAT="${*:-list att gemm conv}"
-export B200_PDL=0  # captures run fully serialised launches (an ncu replay of conv_stem_kernel failed under programmatic dependent launch)
 CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
 $CMD > gpurun_out/bench_small.json 2> gpurun_out/bench_small.err || { echo "plain run failed"; tail -5 gpurun_out/bench_small.err; exit 1; }
 cap() {  # name, regex, skip, count
