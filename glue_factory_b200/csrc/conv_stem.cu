@@ -89,6 +89,28 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const int total_tiles = p.B * tiles_per_img;  // < 2^31, checked by the launcher
+    // Tile coordinates advance by the grid stride as a mixed-radix addition: the two integer divisions of a fresh
+    // decomposition (~65 dependent instructions with MUFU.RCP / F2I) sat on the per-tile critical path of the worker
+    // and epilogue warps (a quarter of the workers' stall samples in the ncu source page).
+    struct StTile {
+        int b, ty, tx;
+    };
+    auto decomp = [&](int t) {
+        StTile c;
+        c.b = t / tiles_per_img;
+        const int rem = t - c.b * tiles_per_img;
+        c.ty = rem / p.tiles_x;
+        c.tx = rem - c.ty * p.tiles_x;
+        return c;
+    };
+    const StTile tile_step = decomp((int)gridDim.x);
+    auto advance = [&](StTile& c) {
+        c.tx += tile_step.tx;
+        c.ty += tile_step.ty;
+        c.b += tile_step.b;
+        if (c.tx >= p.tiles_x) { c.tx -= p.tiles_x; ++c.ty; }
+        if (c.ty >= p.tiles_y) { c.ty -= p.tiles_y; ++c.b; }
+    };
 
     if (warp == 0 && lane == 0) {
         prefetch_tensormap(&tmap_w);
@@ -188,10 +210,9 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         int acc = 0;
         uint32_t acc_phase = 0;
         uint32_t r[32];
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-            const int b = t / tiles_per_img;
-            const int rem = t - b * tiles_per_img;
-            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+        StTile tc = decomp((int)blockIdx.x);
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
+            const int b = tc.b, ty = tc.ty, tx = tc.tx;
             mbar_wait(acc_full + acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * 64 + ((uint32_t)(quarter * 32) << 16);
@@ -298,10 +319,8 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         const bool builder = quarter >= 2;
         const int bt = (((warp - 6) >> 2) * 2 + (quarter - 2)) * 32 + lane;
         // gray pixel e (of 20 x 12) under the patch of tile t, zero outside the image
-        auto load_img = [&](int t, int e) {
-            const int b = t / tiles_per_img;
-            const int rem = t - b * tiles_per_img;
-            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+        auto load_img = [&](const StTile& c, int e) {
+            const int b = c.b, ty = c.ty, tx = c.tx;
             const float* base = p.img + (long long)b * p.C * plane;
             const int iy = e / kStImgW, ix = e - iy * kStImgW;
             const int yy = ty * kStTileH - 2 + iy, xx = tx * kStTileW - 2 + ix;
@@ -351,23 +370,24 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             if (lane == 0) mbar_arrive(a_full + par);
         };
         float nxt0 = 0.f, nxt1 = 0.f;
+        StTile cur = decomp((int)blockIdx.x);  // tile t of the loop below
+        StTile pf = cur;                       // tile whose image pixels are requested next
         if (builder && blockIdx.x < total_tiles) {
-            sImg[bt] = load_img(blockIdx.x, bt);
-            sImg[bt + 128] = load_img(blockIdx.x, bt + 128);
+            sImg[bt] = load_img(pf, bt);
+            sImg[bt + 128] = load_img(pf, bt + 128);
             st_build_bar();
             im2col(sImg, 0);
+            advance(pf);
             if (blockIdx.x + gridDim.x < total_tiles) {
-                nxt0 = load_img(blockIdx.x + gridDim.x, bt);
-                nxt1 = load_img(blockIdx.x + gridDim.x, bt + 128);
+                nxt0 = load_img(pf, bt);
+                nxt1 = load_img(pf, bt + 128);
             }
         }
         uint32_t r[32];
         int i = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i, advance(cur)) {
             const int st = i & 1;
-            const int b = t / tiles_per_img;
-            const int rem = t - b * tiles_per_img;
-            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+            const int ty = cur.ty, tx = cur.tx;
             const int y0 = ty * kStTileH - 1, x0 = tx * kStTileW - 1;  // image position of patch pixel (0, 0)
             // ---- next tile first: its stem GEMM then runs while this tile's patch is written ----
             if (builder && t + gridDim.x < total_tiles) {
@@ -375,9 +395,10 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                 sImg[(st ^ 1) * 256 + bt + 128] = nxt1;
                 st_build_bar();  // the next tile's image pixels are staged
                 im2col(sImg + (st ^ 1) * 256, st ^ 1);
+                advance(pf);  // tile t + 2 grid strides
                 if (t + 2 * gridDim.x < total_tiles) {  // in flight for a whole tile
-                    nxt0 = load_img(t + 2 * gridDim.x, bt);
-                    nxt1 = load_img(t + 2 * gridDim.x, bt + 128);
+                    nxt0 = load_img(pf, bt);
+                    nxt1 = load_img(pf, bt + 128);
                 }
             }
             mbar_wait(c1_full + st, (uint32_t)((i >> 1) & 1));  // stem GEMM of this tile retired
