@@ -70,6 +70,26 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const long long total_tiles = (long long)p.batch * tiles_per_img;
+    // tile coordinates advance by the grid stride as a mixed-radix addition instead of divisions per tile
+    struct CTile {
+        int b, ty, tx;
+    };
+    auto decomp = [&](long long t) {
+        CTile c;
+        c.b = (int)(t / tiles_per_img);
+        const int rem = (int)(t - (long long)c.b * tiles_per_img);
+        c.ty = rem / p.tiles_x;
+        c.tx = rem - c.ty * p.tiles_x;
+        return c;
+    };
+    const CTile tile_step = decomp((long long)gridDim.x);
+    auto advance = [&](CTile& c) {
+        c.tx += tile_step.tx;
+        c.ty += tile_step.ty;
+        c.b += tile_step.b;
+        if (c.tx >= p.tiles_x) { c.tx -= p.tiles_x; ++c.ty; }
+        if (c.ty >= p.tiles_y) { c.ty -= p.tiles_y; ++c.b; }
+    };
 
     if (warp == 0 && lane == 0) {
         prefetch_tensormap(&tmap_a);
@@ -99,10 +119,9 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             for (int tap = 0; tap < 9; ++tap) tma_load_2d(sW + tap * Cfg::kWTapBytes, &tmap_w, w_full, tap * 64, 0);
             int stage = 0;
             uint32_t phase = 0;
-            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-                const int b = (int)(t / tiles_per_img);
-                const int rem = (int)(t - (long long)b * tiles_per_img);
-                const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+            CTile tc = decomp((long long)blockIdx.x);
+            for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
+                const int b = tc.b, ty = tc.ty, tx = tc.tx;
                 mbar_wait(empty_bar + stage, phase ^ 1);
                 mbar_arrive_expect_tx(full_bar + stage, kCpPatchBytes);
                 tma_load_4d(sA + stage * kCpPatchBytes, &tmap_a, full_bar + stage, 0, tx * kCpTileW - 1,
@@ -164,10 +183,9 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         uint32_t acc_phase = 0;
         uint32_t r[32];
         __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out16);
-        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-            const int b = (int)(t / tiles_per_img);
-            const int rem = (int)(t - (long long)b * tiles_per_img);
-            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+        CTile tc = decomp((long long)blockIdx.x);
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
+            const int b = tc.b, ty = tc.ty, tx = tc.tx;
             mbar_wait(acc_full + acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + acc * COUT + ((uint32_t)(quarter * 32) << 16);

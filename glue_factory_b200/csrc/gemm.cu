@@ -560,6 +560,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int n_tiles = EPI == EPI_LN_GELU ? 1 : (p.N + BLOCK_N - 1) / BLOCK_N;
     const long long total_tiles = (long long)p.batch * m_tiles * n_tiles;
     const int k_blocks = p.K / kBlockK;
+    // tile coordinates advance by the grid stride as a mixed-radix addition (a fresh decomposition costs 64-bit
+    // divisions per tile in the producer and in every epilogue warp)
+    struct GTile {
+        int nt, mt, b;
+    };
+    auto decomp = [&](long long t) {
+        GTile c;
+        c.nt = (int)(t % n_tiles);
+        const long long rest = t / n_tiles;
+        c.mt = (int)(rest % m_tiles);
+        c.b = (int)(rest / m_tiles);
+        return c;
+    };
+    const GTile tile_step = decomp((long long)gridDim.x);
+    auto advance = [&](GTile& c) {
+        c.nt += tile_step.nt;
+        c.mt += tile_step.mt;
+        c.b += tile_step.b;
+        if (c.nt >= n_tiles) { c.nt -= n_tiles; ++c.mt; }
+        if (c.mt >= m_tiles) { c.mt -= m_tiles; ++c.b; }
+    };
 
     if (warp == 0 && lane == 0) {
         prefetch_tensormap(&tmap_a);
@@ -588,11 +609,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const bool leader = elect_one();
         int stage = 0;
         uint32_t phase = 0;
-        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-            const int nt = (int)(t % n_tiles);
-            const long long rest = t / n_tiles;
-            const int mt = (int)(rest % m_tiles);
-            const int b = (int)(rest / m_tiles);
+        GTile tc = decomp((long long)blockIdx.x);
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
+            const int nt = tc.nt, mt = tc.mt, b = tc.b;
             for (int hh = 0; hh < kHalves; ++hh) {
             const int brow = b * p.b_batch_rows + (nt * kHalves + hh) * BLOCK_N;
             for (int kb = 0; kb < k_blocks; ++kb) {
@@ -685,11 +704,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const int r_in_tile = quarter * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-            const int nt = (int)(t % n_tiles);
-            const long long rest = t / n_tiles;
-            const int mt = (int)(rest % m_tiles);
-            const int b = (int)(rest / m_tiles);
+        GTile tc = decomp((long long)blockIdx.x);
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
+            const int nt = tc.nt, mt = tc.mt, b = tc.b;
             if constexpr (EPI == EPI_LN_GELU) {
                 // accumulator stage h holds columns [256 h, 256 h + 256) of this row tile; both stages turn over once
                 // per tile, so one phase bit serves both.  `half` is this warp's column group (0..3) here.
