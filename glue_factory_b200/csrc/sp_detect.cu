@@ -27,7 +27,7 @@ namespace b200 {
 #endif
 constexpr int kEW = 128, kEH = NMS_EH, kSeg = 16;
 #ifndef NMS_THREADS
-#define NMS_THREADS 512
+#define NMS_THREADS 768
 #endif
 constexpr int kNmsFastThreads = NMS_THREADS;
 constexpr int kMaskWords = 6;  // [guard | 4 words = 128 columns | guard]
