@@ -115,35 +115,150 @@ def dist_env():
 # CPU arm: the oracle port (oracle/ is a torch-CPU fp32 restatement of the reference, pinned against
 # reference-generated vectors; the reference itself cannot travel to the GPU box)
 # ---------------------------------------------------------------------------------------------
-def oracle_pair_fn():
+SP_ORACLE_CONF = dict(max_num_keypoints=KPTS, detection_threshold=-1, nms_radius=3)
+
+
+def oracle_batch_fn(device="cpu"):
+    """The oracle port on `device` for a batch of pairs: SuperPoint-open on both views, then LightGlue
+    (what TwoViewPipeline does in the reference, two_view_pipeline.py:72-90)."""
     from oracle import lightglue as olg
     from oracle import sp_open as osp
 
-    sp_sd, lg_sd = synth.superpoint_open_state_dict(), synth.lightglue_state_dict()
-    sp_conf = dict(max_num_keypoints=KPTS, detection_threshold=-1, nms_radius=3)
-    size = torch.tensor([[float(W), float(H)]])
+    sp_sd = {k: v.to(device) for k, v in synth.superpoint_open_state_dict().items()}
+    lg_sd = {k: v.to(device) for k, v in synth.lightglue_state_dict().items()}
 
     def run(im0, im1):
+        size = torch.tensor([[float(W), float(H)]] * im0.shape[0], device=device)
         with torch.no_grad():
-            p0 = osp.forward(sp_sd, im0[None], sp_conf)
-            p1 = osp.forward(sp_sd, im1[None], sp_conf)
-            return olg.forward(lg_sd, p0["keypoints"], p1["keypoints"], p0["descriptors"], p1["descriptors"],
-                               size, size, dict(filter_threshold=0.1))
+            p0 = osp.forward(sp_sd, im0, SP_ORACLE_CONF)
+            p1 = osp.forward(sp_sd, im1, SP_ORACLE_CONF)
+            lg = olg.forward(lg_sd, p0["keypoints"], p1["keypoints"], p0["descriptors"], p1["descriptors"],
+                             size, size, dict(filter_threshold=0.1))
+        return p0, p1, lg
 
     return run
 
 
-def time_cpu(num_pairs, warmup_pairs):
+def time_cpu(num_pairs, warmup_pairs, batch=1, keep=0):
+    """Times the oracle port on the host cores: `num_pairs` pairs in steps of `batch` pairs.
+    Returns (pairs/s, seconds, threads, [(p0, p1, lg) of the first `keep` timed steps])."""
     torch.set_num_threads(os.cpu_count() or 1)
-    run = oracle_pair_fn()
-    im0, im1 = make_pairs(0, min(8, max(1, num_pairs)))
-    for i in range(warmup_pairs):
-        run(im0[i % len(im0)], im1[i % len(im0)])
+    run = oracle_batch_fn("cpu")
+    im0, im1 = make_pairs(0, min(8, max(batch, num_pairs)))
+    n = im0.shape[0]
+
+    def chunk(i):
+        idx = [(i * batch + j) % n for j in range(batch)]
+        return im0[idx], im1[idx]
+
+    for i in range(-(-warmup_pairs // batch)):
+        run(*chunk(i))
+    kept = []
+    steps = max(1, num_pairs // batch)
     t0 = time.perf_counter()
-    for i in range(num_pairs):
-        run(im0[i % len(im0)], im1[i % len(im0)])
+    for i in range(steps):
+        out = run(*chunk(i))
+        if i < keep:
+            kept.append(out)
     dt = time.perf_counter() - t0
-    return num_pairs / dt, dt, torch.get_num_threads()
+    return steps * batch / dt, dt, torch.get_num_threads(), kept
+
+
+def time_eager_gpu(dev, im0, im1, steps, warmup, chunk=8):
+    """GPU-library baseline: the same reference algorithm through PyTorch eager on this
+    B200 (cuDNN / cuBLAS / ATen kernels), i.e. the oracle port fed CUDA tensors.  One step = the same 32 resident
+    pairs as the B200 arm, run in chunks of `chunk` pairs (the fp32 full-resolution activations of 64 images
+    would need > 50 GB).  Timed with CUDA events; returns one record per numeric mode."""
+    run = oracle_batch_fn(dev)
+    out = []
+    P = im0.shape[0]
+
+    def step():
+        for c in range(0, P, chunk):
+            run(im0[c:c + chunk], im1[c:c + chunk])
+
+    for name, tf32, autocast in (("fp32", False, False), ("tf32", True, False), ("bf16-autocast", True, True)):
+        old = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+        torch.backends.cuda.matmul.allow_tf32 = tf32
+        torch.backends.cudnn.allow_tf32 = tf32
+        try:
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                for _ in range(warmup):
+                    step()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(steps):
+                    step()
+                e1.record()
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out.append({"dtype": name, "value": P / (ms * 1e-3), "unit": "pairs/s", "ms_per_step": ms})
+        except Exception as e:  # a library failure must not lose the B200 line
+            out.append({"dtype": name, "error": f"{type(e).__name__}: {e}"[:200]})
+        finally:
+            torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+        torch.cuda.empty_cache()
+    return out
+
+
+def _pct(x, q):
+    x = x.flatten().float()
+    k = max(1, min(x.numel(), int(round(q * x.numel()))))
+    return x.kthvalue(k).values.item()
+
+
+def parity_report(pipe, dev, im0, im1, ref):
+    """Achieved parity of the B200 path against the oracle on the pairs the CPU leg just ran (same synthetic
+    pairs, same weights, configs[1] sizes).  `ref` = (p0, p1, lg) oracle predictions of those pairs."""
+    p0, p1, lg = ref
+    B = im0.shape[0]
+    size = torch.tensor([[float(W), float(H)]] * B, device=dev)
+    views = {"view0": {"image": im0.to(dev), "image_size": size}, "view1": {"image": im1.to(dev), "image_size": size}}
+    with torch.no_grad():
+        pred = pipe(views)
+        matcher = pipe.matcher
+        tf = matcher({"keypoints0": p0["keypoints"].to(dev), "keypoints1": p1["keypoints"].to(dev),
+                      "descriptors0": p0["descriptors"].to(dev), "descriptors1": p1["descriptors"].to(dev),
+                      "view0": {"image_size": size}, "view1": {"image_size": size}})
+        fin = matcher.assign_from_descriptors(lg["ref_descriptors0"][:, 0].to(dev), lg["ref_descriptors1"][:, 0].to(dev))
+    out = {"pairs": B, "against": "oracle port (fp32, CPU) on the same pairs and weights"}
+    heat = pred["heatmap0"].cpu()
+    out["heatmap_max_abs_err_over_max"] = ((heat - p0["heatmap"]).abs().max() / p0["heatmap"].max()).item()
+    overlap, e2e_hits, e2e_total = [], 0, 0
+    for b in range(B):
+        ours0 = {tuple(k): i for i, k in enumerate(pred["keypoints0"][b].cpu().tolist())}
+        ours1 = [tuple(k) for k in pred["keypoints1"][b].cpu().tolist()]
+        ref0 = [tuple(k) for k in p0["keypoints"][b].tolist()]
+        ref1 = [tuple(k) for k in p1["keypoints"][b].tolist()]
+        overlap.append(len(set(ours0) & set(ref0)) / len(ref0))
+        m_ours, m_ref = pred["matches0"][b].cpu().tolist(), lg["matches0"][b].tolist()
+        for i, j in enumerate(m_ref):  # end to end: the reference's matches, found again by coordinates
+            if j < 0:
+                continue
+            e2e_total += 1
+            k = ours0.get(ref0[i])
+            if k is not None and m_ours[k] >= 0 and ours1[m_ours[k]] == ref1[j]:
+                e2e_hits += 1
+    out["keypoint_set_overlap"] = sum(overlap) / B
+    out["e2e_reference_matches_reproduced"] = e2e_hits / max(1, e2e_total)
+    out["reference_matches_per_pair"] = e2e_total / B
+    # matcher teacher-forced on the oracle's keypoints / descriptors (bf16 operands through 9 layers)
+    la, la_ref = tf["log_assignment"].cpu(), lg["log_assignment"]
+    rel = (la - la_ref).abs() / la_ref.abs().clamp_min(1e-3)
+    out["teacher_forced_matcher"] = {
+        "match_agreement": (tf["matches0"].cpu() == lg["matches0"]).float().mean().item(),
+        "log_assignment_rel_err": {"median": rel.median().item(), "p99": _pct(rel, 0.99), "max": rel.max().item()},
+        "ref_descriptors_rel_l2": ((tf["ref_descriptors0"].cpu() - lg["ref_descriptors0"]).norm()
+                                   / lg["ref_descriptors0"].norm()).item(),
+    }
+    # final stage teacher-forced on the oracle's last-layer descriptors (fp32-grade split GEMMs): 1e-3 target
+    rel = (fin[0].cpu() - la_ref).abs() / la_ref.abs().clamp_min(1e-3)
+    out["teacher_forced_assignment"] = {
+        "match_agreement": (fin[1].cpu() == lg["matches0"]).float().mean().item(),
+        "log_assignment_rel_err": {"median": rel.median().item(), "p99": _pct(rel, 0.99), "max": rel.max().item()},
+    }
+    return out
 
 
 def run_reference(args):
@@ -151,14 +266,16 @@ def run_reference(args):
     if rank != 0:
         return
     steps, warmup = args.steps, args.warmup
-    pps, dt, cores = time_cpu(steps, warmup)
-    sample = f"{steps} timed step(s) of 1 pair each (1024x1024, 2048 kpts, fp32) after {warmup} warm-up pair(s)"
+    batch = max(1, args.cpu_batch)
+    pps, dt, cores, _ = time_cpu(steps * batch, warmup * batch, batch=batch)
+    sample = (f"{steps} timed step(s) of {batch} pair(s) each (1024x1024, 2048 kpts, fp32) after {warmup} warm-up "
+              f"step(s); one process with {cores} torch threads whatever --gpus says")
     line = {
         "impl": "reference", "metric": METRIC, "value": pps, "unit": "pairs/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": 1000.0 * dt / steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "configs[1]: SP-open + LightGlue, 2048 kpts, 1024x1024 synthetic pairs; "
-                               "CPU arm runs 1 pair per step", "pairs_per_step": 1},
+                               f"CPU arm runs {batch} pair(s) per step", "pairs_per_step": batch},
         "cpu_baseline": {"value": pps, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": pps, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -353,11 +470,26 @@ def run_b200(args):
                                  "timed region", "ms_per_step": ms_profiled / steps, "dominant": ranked[0][0]},
             "gather_ms": gather_ms,
         }
+        if world == 1 and not args.no_gpu_baseline:
+            del dev_in
+            torch.cuda.empty_cache()
+            line["gpu_library_baseline"] = {
+                "kind": "torch-eager", "what": "the oracle port (= the reference algorithm, plain torch ops) on CUDA "
+                "tensors of this B200: cuDNN / cuBLAS / ATen kernels, same 32 resident pairs per step in chunks of 8",
+                "steps": 3, "warmup": 3, "modes": time_eager_gpu(dev, resident["view0"]["image"],
+                                                                 resident["view1"]["image"], 3, 3)}
         if world == 1 and not args.no_cpu_baseline:
-            pps, dt, cores = time_cpu(2, 1)
+            pps, dt, cores, kept = time_cpu(10, 1, batch=1, keep=2)
             line["cpu_baseline"] = {"value": pps, "unit": "pairs/s", "cores": cores, "kind": "port",
-                                    "sample": "2 timed pairs after 1 warm-up pair of the same workload (1024x1024, 2048 kpts), "
-                                              "oracle port, fp32"}
+                                    "sample": "10 timed pairs (batch 1, as eval/hpatches.py:32 runs it) after 1 warm-up pair "
+                                              "of the same workload (1024x1024, 2048 kpts), oracle port, fp32"}
+            pps8, dt8, _, _ = time_cpu(8, 0, batch=8)
+            line["cpu_baseline"]["batch8"] = {"value": pps8, "unit": "pairs/s", "sample": "1 timed step of 8 pairs"}
+            # parity of the B200 arm on the two pairs the CPU leg just computed (oracle = checker only)
+            cat = lambda i, key: torch.cat([k[i][key] for k in kept])  # noqa: E731
+            ref = tuple({key: cat(i, key) for key in kept[0][i] if torch.is_tensor(kept[0][i][key])} for i in range(3))
+            pim0, pim1 = make_pairs(0, 2)
+            line["parity"] = parity_report(pipe, dev, pim0, pim1, ref)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -370,6 +502,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-baseline", action="store_true", help="skip the torch-eager GPU-library baseline")
+    ap.add_argument("--cpu-batch", type=int, default=1, help="--impl reference: pairs per CPU step")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

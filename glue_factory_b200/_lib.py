@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("B200GLUE_LIB") or os.path.join(_HERE, "libb200glue.so
 
 EPI_BIAS_BF16, EPI_QKV_ROTARY, EPI_LN_GELU, EPI_RESID, EPI_F32 = 0, 1, 2, 3, 4
 EPI_CONV_RELU_BN, EPI_CONV_BN_L2, EPI_CONV_BN_SOFTMAX_D2S = 5, 6, 7
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class GemmDesc(C.Structure):

@@ -130,14 +130,12 @@ static int env_int(const char* name, int dflt) {
     return v ? atoi(v) : dflt;
 }
 
-static int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 0;
-    }
-    return n;
+static int sm_count() {  // of the current device
+    static int n[kMaxDevices] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 0;
+    if (n[dev] == 0 && cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n[dev] = 0;
+    return n[dev];
 }
 
 }  // namespace b200
@@ -339,7 +337,6 @@ int b200_lg_assignment(const float* sim, const float* z0, const float* z1, int B
     return launch_assignment(sim, z0, z1, B, M, N, filter_threshold, workspace, scores, matches0, matches1, mscores0,
                              mscores1, static_cast<cudaStream_t>(stream));
 }
-
 int b200_sg_keypoint_encoder_head(const float* keypoints, const float* scores, const float* image_size, int B, int n,
                                   const float* w1, const float* b1, const float* w2, const float* b2, void* out,
                                   b200_stream_t stream) {

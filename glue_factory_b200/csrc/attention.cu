@@ -476,11 +476,11 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
 
 int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
                      int num_seqs, int max_q_len, int heads, int num_sms, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceSize configured;
+    if (!configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kAttSmemBytes));
-        configured = true;
+        configured.cur() = 1;
     }
     if (num_seqs == 0 || max_q_len == 0) return 0;
     p.q_tiles = (max_q_len + kQPerCta - 1) / kQPerCta;

@@ -34,6 +34,20 @@ void set_last_error(const char* fmt, ...);
     } while (0)
 
 // ---------------------------------------------------------------------------------------------
+// per-device host state: function attributes (cudaFuncSetAttribute) and the SM count belong to a device, not to
+// the process, so the "already configured" marks of the launchers are kept per device index
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxDevices = 64;
+inline int current_device_index() {
+    int d = 0;
+    return (cudaGetDevice(&d) == cudaSuccess && d >= 0 && d < kMaxDevices) ? d : 0;
+}
+struct PerDeviceSize {
+    size_t v[kMaxDevices] = {};
+    size_t& cur() { return v[current_device_index()]; }
+};
+
+// ---------------------------------------------------------------------------------------------
 // programmatic dependent launch: a kernel launched with launch_pdl() may become resident while its predecessor
 // in the stream is still running; it runs its prologue (barrier init, TMEM allocation, descriptor prefetch),
 // then pdl_wait() blocks until the predecessor grid has completed and its writes are visible.  Every kernel

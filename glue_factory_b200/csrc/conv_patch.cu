@@ -260,10 +260,10 @@ static int launch_conv_patch_t(const CUtensorMap& ta, const CUtensorMap& tw, con
                                cudaStream_t stream) {
     using Cfg = ConvPatchCfg<COUT>;
     auto kern = conv_patch_kernel<COUT>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceSize configured;
+    if (!configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-        configured = true;
+        configured.cur() = 1;
     }
     const long long total = (long long)p.batch * p.tiles_x * p.tiles_y;
     if (total == 0) return 0;

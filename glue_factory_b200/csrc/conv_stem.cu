@@ -439,10 +439,10 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
 }
 
 int launch_conv_stem(const CUtensorMap& tw, const StemParams& p, int num_sms, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceSize configured;
+    if (!configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(conv_stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStSmemBytes));
-        configured = true;
+        configured.cur() = 1;
     }
     const long long total = (long long)p.B * p.tiles_x * p.tiles_y;
     if (total == 0) return 0;

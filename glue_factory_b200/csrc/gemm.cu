@@ -784,10 +784,10 @@ static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmPa
                       cudaStream_t stream) {
     using Cfg = GemmCfg<BLOCK_N, EPI>;
     auto kern = gemm_tcgen05_kernel<BLOCK_N, EPI, A_MODE>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceSize configured;
+    if (!configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-        configured = true;
+        configured.cur() = 1;
     }
     const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
     const int n_tiles = EPI == EPI_LN_GELU ? 1 : (p.N + BLOCK_N - 1) / BLOCK_N;  // LayerNorm: one CTA per row tile

@@ -236,10 +236,10 @@ static int launch_nms_fast(const float* scores, int B, int H, int W, int pad, co
                            unsigned long long* cand, int* cand_count, int cap, cudaStream_t stream) {
     using G = NmsGeom<R>;
     auto kern = nms_list_kernel<R>;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceSize configured;
+    if (!configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::kSmemBytes));
-        configured = true;
+        configured.cur() = 1;
     }
     dim3 grid((W + G::kTileW - 1) / G::kTileW, (H + G::kTileH - 1) / G::kTileH, B);
     kern<<<grid, kNmsFastThreads, G::kSmemBytes, stream>>>(scores, H, W, pad, image_hw, out, cand, cand_count, cap);
@@ -320,7 +320,10 @@ select_list_kernel(const float* __restrict__ map, int H, int W, float thr, int k
     while (P < count) P <<= 1;
     for (int i = tid; i < P; i += kListThreads) keys[i] = 0ull;
     __syncthreads();
-    const bool by_index = n <= k;
+    // fewer candidates than k: the reference returns them in row-major order (no top-k call).  With a negative
+    // threshold the reference's candidate set is every interior pixel, i.e. always more than k, and its
+    // top-k sorts by score: n == k positive maxima then still come out score-descending.
+    const bool by_index = thr >= 0.f && n <= k;
     if (by_index) {
         for (int i = tid; i < n_raw; i += kListThreads) {
             const unsigned long long e = list[i];
@@ -410,10 +413,10 @@ int launch_select_list(const float* nms_map, int B, int H, int W, float threshol
     int P = 1;
     while (P < k) P <<= 1;
     const size_t smem = (size_t)P * sizeof(unsigned long long);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static PerDeviceSize configured;
+    if (smem > configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(select_list_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        configured.cur() = smem;
     }
     select_list_kernel<<<B, kListThreads, smem, stream>>>(nms_map, H, W, threshold, k, cand, cand_count, cap, kpts,
                                                           kscores, kidx, counts);

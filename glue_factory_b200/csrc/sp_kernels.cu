@@ -194,10 +194,10 @@ int launch_nms_border(const float* scores, int B, int H, int W, int radius, int 
     const int E = kNmsTile + 10 * radius;
     const size_t smem = (size_t)E * E * 10;
     B200_REQUIRE(smem <= 227 * 1024, "nms: radius %d needs %zu bytes of shared memory (max 232448)", radius, smem);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static PerDeviceSize configured;
+    if (smem > configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(nms_border_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        configured.cur() = smem;
     }
     dim3 grid((W + kNmsTile - 1) / kNmsTile, (H + kNmsTile - 1) / kNmsTile, B);
     nms_border_kernel<<<grid, kNmsThreads, smem, stream>>>(scores, H, W, radius, pad, out);

@@ -201,10 +201,10 @@ int launch_select_topk_flagged(const float* nms_map, int B, int H, int W, float 
     int P = 1;
     while (P < k) P <<= 1;
     const size_t smem = (size_t)P * sizeof(unsigned long long);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static PerDeviceSize configured;
+    if (smem > configured.cur()) {
         B200_CHECK_CUDA(cudaFuncSetAttribute(select_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        configured.cur() = smem;
     }
     select_topk_kernel<<<B, kSelThreads, smem, stream>>>(nms_map, H, W, threshold, k, kpts, kscores, kidx, counts,
                                                          only_flagged);

@@ -33,8 +33,8 @@ def adaptive_forward(model, data, kpts0, kpts1, desc0, desc1, size0, size1):
     alt = {k: torch.empty_like(ws[k]) for k in ("x32", "xm", "cs")}  # compaction target (ping-pong)
     ops.lg_ingest(desc0, ws["x32"], ws["xm"], 512, row0=0)
     ops.lg_ingest(desc1, ws["x32"], ws["xm"], 512, row0=M)
-    ops.lg_posenc(kpts0.float().contiguous(), _size(size0, dev), P["wr"], ws["cs"], row0=0)
-    ops.lg_posenc(kpts1.float().contiguous(), _size(size1, dev), P["wr"], ws["cs"], row0=M)
+    ops.lg_posenc(kpts0.float().contiguous(), _size(size0, dev, 1), P["wr"], ws["cs"], row0=0)
+    ops.lg_posenc(kpts1.float().contiguous(), _size(size1, dev, 1), P["wr"], ws["cs"], row0=M)
 
     ind = torch.cat([torch.arange(M, dtype=torch.int32), torch.arange(N, dtype=torch.int32)]).to(dev)
     ind_alt = torch.empty_like(ind)

@@ -59,6 +59,7 @@ class NearestNeighborMatcher(BaseModel):
                  out32=sim, ld32=N, out32_batch_stride=M * N)
         return sim
 
+    @ops.on_device("descriptors0")
     def _forward(self, data):
         c = self.conf
         if c.ratio_thresh and min(data["descriptors0"].shape[1], data["descriptors1"].shape[1]) < 2:

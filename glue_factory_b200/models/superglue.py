@@ -24,24 +24,28 @@ from torch import nn
 from gluefactory.models.base_model import BaseModel
 
 from .. import ops
+from .lightglue import _size
 
 
-def MLP(channels, do_bn=True):
-    layers = []
-    for i in range(1, len(channels)):
-        layers.append(nn.Conv1d(channels[i - 1], channels[i], kernel_size=1, bias=True))
-        if i < len(channels) - 1:
-            if do_bn:
-                layers.append(nn.BatchNorm1d(channels[i]))
-            layers.append(nn.ReLU())
-    return nn.Sequential(*layers)
+def _pointwise_stack(widths, norm=True):
+    """Stack of 1x1 Conv1d layers held in an nn.Sequential whose child indices give the checkpoint key names:
+    a hidden layer takes the slots (conv, [BatchNorm1d], ReLU), the output layer a single conv slot."""
+    table = {}
+    pairs = list(zip(widths[:-1], widths[1:]))
+    for li, (c_in, c_out) in enumerate(pairs):
+        table[len(table)] = nn.Conv1d(c_in, c_out, 1)
+        if li + 1 < len(pairs):
+            if norm:
+                table[len(table)] = nn.BatchNorm1d(c_out)
+            table[len(table)] = nn.ReLU()
+    return nn.Sequential(*(table[i] for i in range(len(table))))
 
 
 class KeypointEncoder(nn.Module):
     def __init__(self, feature_dim, layers, use_scores=True):
         super().__init__()
         self.use_scores = use_scores
-        self.encoder = MLP([3 if use_scores else 2] + list(layers) + [feature_dim])
+        self.encoder = _pointwise_stack([3 if use_scores else 2, *layers, feature_dim])
         nn.init.constant_(self.encoder[-1].bias, 0.0)
 
 
@@ -57,7 +61,7 @@ class AttentionalPropagation(nn.Module):
     def __init__(self, num_dim, num_heads):
         super().__init__()
         self.attn = MultiHeadedAttention(num_heads, num_dim)
-        self.mlp = MLP([num_dim * 2, num_dim * 2, num_dim])
+        self.mlp = _pointwise_stack([2 * num_dim, 2 * num_dim, num_dim])
         nn.init.constant_(self.mlp[-1].bias, 0.0)
 
 
@@ -148,6 +152,7 @@ class SuperGlue(BaseModel):
         self._packed, self._packed_key = P, key
         return P
 
+    @ops.on_device("keypoints0")
     def _forward(self, data):
         kpts0, kpts1 = data["keypoints0"], data["keypoints1"]
         if kpts0.shape[1] == 0 or kpts1.shape[1] == 0:  # no keypoints
@@ -170,8 +175,8 @@ class SuperGlue(BaseModel):
             size = view.get("image_size")
             if size is None:
                 _, _, h, w = view["image"].shape
-                size = torch.tensor([[float(w), float(h)]] * B)
-            return size.to(device=dev, dtype=torch.float32).contiguous()
+                size = [float(w), float(h)]
+            return _size(size, dev, B)  # broadcast to [B, 2] as the kernel indexes it
 
         size0, size1 = size_of(data["view0"]), size_of(data["view1"])
         bf = torch.bfloat16

@@ -45,11 +45,13 @@ class SuperPoint(BaseModel):
             raise NotImplementedError("the B200 kernels are built for the full model with descriptor_dim 256")
         if conf.refinement_radius > 0:
             raise NotImplementedError("soft-argmax refinement is outside the B200 path")
-        c1, c2, c3, c4, c5 = 64, 64, 128, 128, 256
-        for name, ci, co, k in (("conv1a", 1, c1, 3), ("conv1b", c1, c1, 3), ("conv2a", c1, c2, 3), ("conv2b", c2, c2, 3),
-                                ("conv3a", c2, c3, 3), ("conv3b", c3, c3, 3), ("conv4a", c3, c4, 3), ("conv4b", c4, c4, 3),
-                                ("convPa", c4, c5, 3), ("convPb", c5, 65, 1), ("convDa", c4, c5, 3),
-                                ("convDb", c5, conf.descriptor_dim, 1)):
+        # checkpoint layer names -> (in, out, kernel): the VGG topology of the kernels (two 64-wide and two 128-wide
+        # stages, 256-wide heads)
+        layout = {"conv1a": (1, 64, 3), "conv1b": (64, 64, 3), "conv2a": (64, 64, 3), "conv2b": (64, 64, 3),
+                  "conv3a": (64, 128, 3), "conv3b": (128, 128, 3), "conv4a": (128, 128, 3), "conv4b": (128, 128, 3),
+                  "convPa": (128, 256, 3), "convPb": (256, 65, 1), "convDa": (128, 256, 3),
+                  "convDb": (256, conf.descriptor_dim, 1)}
+        for name, (ci, co, k) in layout.items():
             setattr(self, name, nn.Conv2d(ci, co, kernel_size=k, stride=1, padding=(k - 1) // 2))
         # the reference always fetches the MagicLeap checkpoint (superpoint.py:198-200); an optional local
         # `weights` path is accepted in addition so that the model can be built offline
@@ -99,6 +101,7 @@ class SuperPoint(BaseModel):
     def dense_forward(self, image):
         return sp_dense_forward(self._pack(), image)
 
+    @ops.on_device("image")
     def _forward(self, data):
         image = data["image"]
         c = self.conf

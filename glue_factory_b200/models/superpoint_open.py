@@ -195,6 +195,7 @@ class SuperPoint(BaseModel):
         kpts, scores, _, counts = ops.sp_select_topk(nms, c.detection_threshold, k)
         return kpts, scores, counts
 
+    @ops.on_device("image")
     def _forward(self, data):
         image = data["image"]
         heat, dense = self.dense_forward(image)

@@ -20,6 +20,25 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def on_device(key):
+    """Decorator for a model's `_forward(self, data)`: the kernels launch on the CURRENT device's stream and the
+    library keeps per-device launch state, so the device of `data[key]` is made current for the whole pass
+    (a model moved with `.to('cuda:1')` then works whatever the caller's current device is)."""
+
+    def wrap(fn):
+        def inner(self, data):
+            t = data[key]
+            if not t.is_cuda:
+                return fn(self, data)  # the body reports CPU tensors itself (there is no CPU fallback)
+            with torch.cuda.device(t.device):
+                return fn(self, data)
+
+        inner.__name__, inner.__doc__ = fn.__name__, fn.__doc__
+        return inner
+
+    return wrap
+
+
 # ---- launch accounting (bench.py): number of kernels launched, optional CUDA-event timing per tag --
 class _Stats:
     launches = 0
@@ -71,9 +90,17 @@ def _ptr(t, offset_elems: int = 0):
 
 
 def _require_cuda(*tensors):
+    cur = None
     for t in tensors:
-        if t is not None and not t.is_cuda:
+        if t is None:
+            continue
+        if not t.is_cuda:
             raise _lib.B200Error("b200glue kernels need CUDA tensors (there is no CPU fallback)")
+        if cur is None:
+            cur = torch.cuda.current_device()
+        if t.device.index != cur:
+            raise _lib.B200Error(f"tensor on cuda:{t.device.index} but the current device is cuda:{cur}: wrap the call "
+                                 "in torch.cuda.device(tensor.device) (the models' forward does)")
 
 
 def gemm(a, w, *, M, N, K, lda, block_n, epilogue, a_rows=None, a_col0=0, ldb=None, batch=1,

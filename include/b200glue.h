@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 5
+#define B200_ABI_VERSION 6
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -165,7 +165,6 @@ int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, 
                        int B, int M, int N, float filter_threshold, void* workspace,
                        float* scores /*[B,M+1,N+1]*/, long long* matches0, long long* matches1,
                        float* mscores0, float* mscores1, b200_stream_t stream);
-
 
 /* ---- nearest-neighbour matcher (gluefactory/models/matchers/nearest_neighbor_matcher.py) ------ */
 /* fp32 [rows,cols] -> bf16 [rows,3*cols] two-term split feeding a K = 3*cols similarity GEMM with near-fp32

@@ -117,8 +117,8 @@ def filter_matches(scores, th):
     inner = scores[:, :-1, :-1]
     max0, max1 = inner.max(2), inner.max(1)
     m0, m1 = max0.indices, max1.indices
-    i0 = torch.arange(m0.shape[1])[None]
-    i1 = torch.arange(m1.shape[1])[None]
+    i0 = torch.arange(m0.shape[1], device=m0.device)[None]
+    i1 = torch.arange(m1.shape[1], device=m1.device)[None]
     mutual0 = i0 == m1.gather(1, m0)
     mutual1 = i1 == m0.gather(1, m1)
     e0 = max0.values.exp()
@@ -150,7 +150,7 @@ def forward(sd, kpts0, kpts1, desc0, desc1, size0=None, size1=None, conf=None, r
     enc0, enc1 = positional_encoding(sd, k0), positional_encoding(sd, k1)
     early, prune = c["depth_confidence"] > 0, c["width_confidence"] > 0
     if prune:
-        ind0, ind1 = torch.arange(m)[None], torch.arange(n)[None]
+        ind0, ind1 = torch.arange(m, device=kpts0.device)[None], torch.arange(n, device=kpts0.device)[None]
         prune0, prune1 = torch.ones_like(ind0), torch.ones_like(ind1)
     stages = []
     tok0 = tok1 = None
@@ -192,11 +192,11 @@ def forward(sd, kpts0, kpts1, desc0, desc1, size0=None, size1=None, conf=None, r
     scores, sim = log_assignment(sd, i, d0, d1)
     m0, m1, ms0, ms1 = filter_matches(scores, c["filter_threshold"])
     if prune:
-        m0_ = torch.full((b, m), -1, dtype=m0.dtype)
-        m1_ = torch.full((b, n), -1, dtype=m1.dtype)
+        m0_ = torch.full((b, m), -1, dtype=m0.dtype, device=m0.device)
+        m1_ = torch.full((b, n), -1, dtype=m1.dtype, device=m0.device)
         m0_[:, ind0] = torch.where(m0 == -1, -1, ind1.gather(1, m0.clamp(min=0)))
         m1_[:, ind1] = torch.where(m1 == -1, -1, ind0.gather(1, m1.clamp(min=0)))
-        ms0_, ms1_ = torch.zeros(b, m), torch.zeros(b, n)
+        ms0_, ms1_ = torch.zeros(b, m, device=m0.device), torch.zeros(b, n, device=m0.device)
         ms0_[:, ind0] = ms0
         ms1_[:, ind1] = ms1
         m0, m1, ms0, ms1 = m0_, m1_, ms0_, ms1_

@@ -14,4 +14,9 @@ for t in test_linear_bias test_linear_strided test_qkv_rotary test_ffn_layernorm
   run dense_$t 300 tests/test_gpu_dense.py -k $t
 done
 run e2e 900 tests/test_gpu_e2e.py
+run nn 300 tests/test_gpu_nn.py
+run superglue 600 tests/test_gpu_superglue.py
+run extractor_paths 300 tests/test_gpu_extractor_paths.py
+run parity_config 600 tests/test_gpu_parity_config.py
+run zz_no_alloc 300 tests/test_zz_no_alloc.py
 cat gpurun_out/summary.txt

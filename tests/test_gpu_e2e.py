@@ -1,12 +1,13 @@
 """GPU end-to-end parity of the B200 models against the CPU oracle and the reference-generated
 golden vectors, through the public Glue Factory API (get_model / forward(data)).
 
-Tolerances (fp32 oracle vs bf16-operand / fp32-accumulate kernels), stated per tensor:
-  heat map            |d| <= 3e-2 * max      (bf16 conv stack, reported)
-  dense descriptors   cosine >= 0.995         (bf16 conv stack)
-  LightGlue layer out relative L2 <= 3e-2     (bf16 GEMM operands, fp32 residual stream)
-  log_assignment      median |d|/|ref| <= 2e-2
-  match agreement     >= 0.98 teacher-forced on the oracle's keypoints (bf16); reported end to end
+Tolerances (fp32 oracle vs bf16-operand / fp32-accumulate kernels), stated per tensor, with the achieved
+figures of round 2 in brackets (the benchmarked sizes are covered by test_gpu_parity_config.py):
+  heat map            |d| <= 3e-2 * max       [2.3e-2]   (bf16 conv stack)
+  dense descriptors   cosine >= 0.998          [0.9991]   (bf16 conv stack)
+  LightGlue layer out relative L2 <= 1e-2      [6.1e-3 .. 7.1e-3]  (bf16 GEMM operands, fp32 residual stream)
+  log_assignment      median |d|/|ref| <= 3e-3, p99 <= 1.5e-2  [1.5e-3, 8.5e-3]
+  match agreement     >= 0.995 teacher-forced on the oracle's keypoints (north_star)  [0.9961 .. 1.0]
 The teacher-forced stage tests in test_gpu_bandwidth.py carry the bit-exact / 1e-3 claims.
 """
 import os
@@ -51,7 +52,7 @@ def test_superpoint_dense_stages(dev, sp_weights, weight_files):
     print(f"heatmap max err / max = {err:.4f}; dense descriptor cosine min {cos.min().item():.5f} mean {cos.mean().item():.6f}")
     assert heat.shape == ref["heatmap"].shape
     assert err < 3e-2
-    assert cos.min().item() > 0.995
+    assert cos.min().item() > 0.998
 
 
 def test_superpoint_teacher_forced_detection(dev, sp_weights, weight_files):
@@ -99,17 +100,18 @@ def test_lightglue_vs_oracle(dev, lg_weights, weight_files, B, M, N):
     for key in ("ref_descriptors0", "ref_descriptors1"):
         rel = ((pred[key].cpu() - ref[key]).norm() / ref[key].norm()).item()
         print(key, "relative L2", rel)
-        assert rel < 3e-2
+        assert rel < 1e-2
     la, la_ref = pred["log_assignment"].cpu(), ref["log_assignment"]
     assert la.shape == la_ref.shape and la.dtype == torch.float32
     rel = ((la - la_ref).abs() / la_ref.abs().clamp_min(1e-3))
     print("log_assignment relative error: median", rel.median().item(), "p99", rel.flatten().kthvalue(int(rel.numel() * 0.99)).values.item())
-    assert rel.median().item() < 2e-2
+    assert rel.median().item() < 3e-3
+    assert rel.flatten().kthvalue(int(rel.numel() * 0.99)).values.item() < 1.5e-2
     agree = (pred["matches0"].cpu() == ref["matches0"]).float().mean().item()
     matched = ref["matches0"] >= 0
     agree_matched = (pred["matches0"].cpu()[matched] == ref["matches0"][matched]).float().mean().item()
     print(f"match agreement {agree:.4f} (on {matched.sum().item()} reference matches: {agree_matched:.4f})")
-    assert agree >= 0.98
+    assert agree >= 0.995 and agree_matched >= 0.995
     assert pred["matches0"].dtype == torch.int64 and pred["prune0"].dtype == torch.float32
 
 
@@ -138,7 +140,20 @@ def test_pipeline_boat_vs_reference_golden(dev, golden_dir, weight_files):
         got = {tuple(p) for p in pred[f"keypoints{i}"][0].cpu().numpy().tolist()}
         want = {tuple(p) for p in g[f"keypoints{i}"][0].tolist()}
         print(f"view{i}: keypoint set overlap with the reference {len(got & want) / 1024:.4f}")
-        assert len(got & want) / 1024 > 0.85  # bf16 conv stack moves borderline detections
+        assert len(got & want) / 1024 > 0.95  # bf16 conv stack moves borderline detections (achieved 0.968)
+    # matches of the reference pipeline, found again by keypoint coordinates (a match is lost when either end moved)
+    k0 = {tuple(p): i for i, p in enumerate(pred["keypoints0"][0].cpu().numpy().tolist())}
+    k1 = [tuple(p) for p in pred["keypoints1"][0].cpu().numpy().tolist()]
+    m_ours = pred["matches0"][0].cpu().tolist()
+    hits = total = 0
+    for i, j in enumerate(g["matches0"][0].tolist()):
+        if j < 0:
+            continue
+        total += 1
+        a = k0.get(tuple(g["keypoints0"][0][i].tolist()))
+        hits += a is not None and m_ours[a] >= 0 and k1[m_ours[a]] == tuple(g["keypoints1"][0][j].tolist())
+    print(f"reference matches reproduced end to end: {hits}/{total}")
+    assert total > 0 and hits / total > 0.85
 
 
 @pytest.mark.parametrize("name", ["lg_adaptive", "lg_prune_only", "lg_depth_only"])
@@ -158,7 +173,7 @@ def test_lightglue_adaptive_vs_reference_golden(dev, golden_dir, weight_files, n
         pred = model(data)
     # bf16 GEMM operands move matchability / confidence logits by ~1e-2, so a keypoint sitting on a pruning
     # threshold may flip (expected: a few per 320 tokens over 8 layers).  Stated tolerance: the per-keypoint
-    # prune counters agree on >= 97 % of the keypoints and the surviving set differs by <= 2 %; the compaction
+    # prune counters agree on >= 99 % of the keypoints (achieved 100 %) and the surviving set differs by <= 1 %; the compaction
     # kernels themselves are checked bit-exactly in test_gpu_bandwidth.py::test_prune_compaction_bit_exact.
     p0, p1 = pred["prune0"].cpu().numpy(), pred["prune1"].cpu().numpy()
     assert pred["prune0"].dtype == torch.from_numpy(g["prune0"]).dtype
@@ -168,11 +183,11 @@ def test_lightglue_adaptive_vs_reference_golden(dev, golden_dir, weight_files, n
     agree = (pred["matches0"].cpu().numpy() == g["matches0"]).mean()
     print(name, "prune counters equal", same, "kept-count difference", kept_diff, "match agreement", agree,
           "log_assignment", tuple(pred["log_assignment"].shape), g["log_assignment"].shape)
-    assert same >= 0.97 and kept_diff <= 0.02 * (p0.size + p1.size)
+    assert same >= 0.99 and kept_diff <= 0.01 * (p0.size + p1.size)
     assert p0.max() == g["prune0"].max()  # same exit layer
-    assert agree >= 0.95
+    assert agree >= 0.99
     if tuple(pred["log_assignment"].shape) == g["log_assignment"].shape and same == 1.0:
         rel = np.abs(pred["log_assignment"].cpu().numpy() - g["log_assignment"]) / np.maximum(np.abs(g["log_assignment"]), 1e-3)
-        assert np.median(rel) < 2e-2
+        assert np.median(rel) < 3e-3
         rd = pred["ref_descriptors0"].cpu().numpy()
-        assert np.linalg.norm(rd - g["ref_descriptors0"]) / np.linalg.norm(g["ref_descriptors0"]) < 3e-2
+        assert np.linalg.norm(rd - g["ref_descriptors0"]) / np.linalg.norm(g["ref_descriptors0"]) < 1e-2
