@@ -337,6 +337,16 @@ int b200_lg_assignment(const float* sim, const float* z0, const float* z1, int B
     return launch_assignment(sim, z0, z1, B, M, N, filter_threshold, workspace, scores, matches0, matches1, mscores0,
                              mscores1, static_cast<cudaStream_t>(stream));
 }
+size_t b200_lg_assignment_static_capacity(void) { return assignment_static_capacity(); }
+int b200_lg_assignment_static(const float* sim, const float* z0, const float* z1, int B, int M, int N,
+                              float filter_threshold, float* scores, long long* matches0, long long* matches1,
+                              float* mscores0, float* mscores1, b200_stream_t stream) {
+    B200_REQUIRE(sim && z0 && z1 && scores && matches0 && matches1 && mscores0 && mscores1,
+                 "assignment_static: null argument");
+    return launch_assignment_static(sim, z0, z1, B, M, N, filter_threshold, scores, matches0, matches1, mscores0,
+                                    mscores1, static_cast<cudaStream_t>(stream));
+}
+
 int b200_sg_keypoint_encoder_head(const float* keypoints, const float* scores, const float* image_size, int B, int n,
                                   const float* w1, const float* b1, const float* w2, const float* b2, void* out,
                                   b200_stream_t stream) {

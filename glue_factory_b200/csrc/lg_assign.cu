@@ -6,6 +6,9 @@
 // both passes use 64 x 256 tiles with one thread per column, so every global access is coalesced; column
 // statistics stay in registers, row statistics are taken after a transposition through shared memory.
 // (reference: gluefactory/models/matchers/lightglue.py:250-262,265-281,287-303)
+#include <mutex>
+
+#include "../../include/b200glue.h"
 #include "common.cuh"
 #include "lg_kernels.cuh"
 
@@ -323,6 +326,51 @@ int launch_assignment_finalize(const float* sim, float simw, int B, int M, int N
     filter_matches_kernel<<<lin, 256, 0, stream>>>(M, N, threshold, w, m0, m1, ms0, ms1);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+// ---- allocation-free variant of launch_assignment ---------------------------------------------------
+// Callers that cannot provide a workspace (CUDA graph capture, serving loops that forbid cudaMalloc) get the
+// scratch from a file-scope device array instead.  Every GPU that loads the library holds these bytes until
+// exit.  In HOST code `g_assign_scratch` is only a stand-in for the symbol, not a device address: the address
+// is looked up once per device with cudaGetSymbolAddress (device current) and carved like a caller workspace.
+// All calls share the one array and it keeps the previous call's contents; the assignment kernels write every
+// partial / term / arg-max slot before reading it, so nothing has to start at zero.  Calls that overlap on
+// the GPU (two streams, or two host threads on different streams) race on it.
+constexpr size_t kStaticScratchBytes = B200_LG_ASSIGNMENT_STATIC_MAX_BYTES;
+static __device__ __align__(256) unsigned char g_assign_scratch[kStaticScratchBytes];
+
+static void* g_assign_scratch_ptr[kMaxDevices];  // per device, filled on first use
+static std::mutex g_assign_scratch_mu;
+
+static int static_scratch(void** out) {
+    int dev = -1;
+    B200_CHECK_CUDA(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < kMaxDevices, "assignment_static: device index %d is out of range", dev);
+    std::lock_guard<std::mutex> lk(g_assign_scratch_mu);
+    if (g_assign_scratch_ptr[dev] == nullptr) {
+        void* ptr = nullptr;
+        B200_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_assign_scratch));
+        B200_REQUIRE(ptr != nullptr, "assignment_static: cudaGetSymbolAddress returned a null address");
+        g_assign_scratch_ptr[dev] = ptr;
+    }
+    *out = g_assign_scratch_ptr[dev];
+    return 0;
+}
+
+size_t assignment_static_capacity() { return kStaticScratchBytes; }
+
+int launch_assignment_static(const float* sim, const float* z0, const float* z1, int B, int M, int N, float threshold,
+                             float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
+                             cudaStream_t stream) {
+    B200_REQUIRE(B >= 0 && M >= 1 && N >= 1, "assignment_static: bad sizes (B=%d, M=%d, N=%d)", B, M, N);
+    const size_t need = assignment_workspace_bytes(B, M, N);
+    B200_REQUIRE(need <= kStaticScratchBytes,
+                 "assignment_static: B=%d, M=%d, N=%d needs %zu bytes of scratch, the built-in array holds %zu; "
+                 "use b200_lg_assignment with a caller workspace",
+                 B, M, N, need, kStaticScratchBytes);
+    void* ws = nullptr;
+    if (static_scratch(&ws) != 0) return -2;
+    return launch_assignment(sim, z0, z1, B, M, N, threshold, ws, scores, m0, m1, ms0, ms1, stream);
 }
 
 // ---- nearest-neighbour matcher (reference: gluefactory/models/matchers/nearest_neighbor_matcher.py:14-72) ----

@@ -16,6 +16,10 @@ int launch_assignment(const float* sim, const float* z0, const float* z1, int B,
 int launch_assignment_finalize(const float* sim, float simw, int B, int M, int N, float threshold, void* workspace,
                                float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
                                cudaStream_t stream);
+size_t assignment_static_capacity();
+int launch_assignment_static(const float* sim, const float* z0, const float* z1, int B, int M, int N, float threshold,
+                             float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
+                             cudaStream_t stream);
 size_t nn_match_workspace_bytes(int B, int M, int N);
 int launch_nn_match(const float* sim, int B, int M, int N, float ratio_sq, float dist_sq, int mutual, void* workspace,
                     float* scores, long long* m0, long long* m1, float* ms0, float* ms1, cudaStream_t stream);

@@ -166,6 +166,22 @@ int b200_lg_assignment(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, 
                        float* scores /*[B,M+1,N+1]*/, long long* matches0, long long* matches1,
                        float* mscores0, float* mscores1, b200_stream_t stream);
 
+/* Allocation-free variant of b200_lg_assignment.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results as b200_lg_assignment, but the scratch lives in a
+ * file-scope device array of B200_LG_ASSIGNMENT_STATIC_MAX_BYTES inside the library (held by every GPU that loads
+ * it, until exit), so the call performs no cudaMalloc / cudaFree and takes no workspace.  Problems with
+ * b200_lg_assignment_workspace(B, M, N) > B200_LG_ASSIGNMENT_STATIC_MAX_BYTES are rejected (-1, message in
+ * b200_last_error()); 4 MiB covers e.g. B = 4 at 2048 x 2048 or B = 1 at 4096 x 4096 keypoints.  Every call on a
+ * device shares that one array: calls that overlap on the GPU (different streams) race; serialise them.
+ * b200_lg_assignment_static_capacity() returns the limit in bytes. */
+#define B200_LG_ASSIGNMENT_STATIC_MAX_BYTES (4u << 20)
+size_t b200_lg_assignment_static_capacity(void);
+int b200_lg_assignment_static(const float* sim /*[B,M,N]*/, const float* z0 /*[B,M]*/, const float* z1 /*[B,N]*/,
+                              int B, int M, int N, float filter_threshold, float* scores /*[B,M+1,N+1]*/,
+                              long long* matches0, long long* matches1, float* mscores0, float* mscores1,
+                              b200_stream_t stream);
+
 /* ---- nearest-neighbour matcher (gluefactory/models/matchers/nearest_neighbor_matcher.py) ------ */
 /* fp32 [rows,cols] -> bf16 [rows,3*cols] two-term split feeding a K = 3*cols similarity GEMM with near-fp32
  * accuracy (the einsum at :52): rows < split_row: [hi|hi|lo] (A side), the others: [hi|lo|hi] (B side). */
