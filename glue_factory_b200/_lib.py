@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("B200GLUE_LIB") or os.path.join(_HERE, "libb200glue.so
 
 EPI_BIAS_BF16, EPI_QKV_ROTARY, EPI_LN_GELU, EPI_RESID, EPI_F32 = 0, 1, 2, 3, 4
 EPI_CONV_RELU_BN, EPI_CONV_BN_L2, EPI_CONV_BN_SOFTMAX_D2S = 5, 6, 7
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 
 class GemmDesc(C.Structure):
@@ -48,6 +48,14 @@ class AttnDesc(C.Structure):
         ("out", C.c_void_p), ("ld_out", C.c_longlong), ("out_col0", C.c_int),
     ]
 
+
+class ExportField(C.Structure):
+    _fields_ = [("src", C.c_void_p), ("scales", C.c_void_p), ("elems_per_pair", C.c_longlong),
+                ("dst_offset", C.c_longlong), ("kind", C.c_int), ("reserved", C.c_int)]
+
+
+EXPORT_F32, EXPORT_F32_KEYPOINTS, EXPORT_I64 = 0, 1, 2
+EXPORT_MAX_FIELDS = 16
 
 _SIGNATURES = {
     "b200_abi_version": (C.c_int, []),
@@ -94,6 +102,17 @@ _SIGNATURES = {
     "b200_lg_assignment_static_capacity": (C.c_size_t, []),
     "b200_lg_assignment_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_prep_resize": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                   C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                   C.c_void_p]),
+    "b200_export_pack": (C.c_int, [C.POINTER(ExportField), C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_longlong,
+                                   C.c_void_p]),
+    "b200_eval_matches_homography": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                               C.c_void_p, C.c_void_p]),
+    "b200_eval_matches_epipolar": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_eval_homography_dlt": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200_lg_count_below": (C.c_int, [C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "b200_lg_prune": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p,

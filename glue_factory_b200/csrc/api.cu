@@ -11,6 +11,7 @@
 #include "conv_stem.cuh"
 #include "common.cuh"
 #include "gemm.cuh"
+#include "io_kernels.cuh"
 #include "lg_kernels.cuh"
 #include "sp_kernels.cuh"
 
@@ -396,6 +397,35 @@ int b200_lg_scatter_matches(const long long* m0, const long long* m1, const floa
                             float* out_ms1, b200_stream_t stream) {
     return launch_scatter_matches(m0, m1, ms0, ms1, ind, n0, n1, out_m0, out_m1, out_ms0, out_ms1,
                                   static_cast<cudaStream_t>(stream));
+}
+
+int b200_prep_resize(const void* src, int src_kind, int B, int C, int H, int W, int out_h, int out_w, const float* taps_x,
+                     int kx, const float* taps_y, int ky, float* tmp, float* out, int pad_h, int pad_w,
+                     unsigned char* mask, b200_stream_t stream) {
+    const int num_sms = sm_count();
+    B200_REQUIRE(num_sms > 0, "prep_resize: no CUDA device available");
+    return launch_prep_resize(src, src_kind, B, C, H, W, out_h, out_w, taps_x, kx, taps_y, ky, tmp, out, pad_h, pad_w, mask,
+                              num_sms, static_cast<cudaStream_t>(stream));
+}
+int b200_export_pack(const b200_export_field* fields, int num_fields, int B, int as_half, void* records,
+                     long long record_bytes, b200_stream_t stream) {
+    return launch_export_pack(fields, num_fields, B, as_half, records, record_bytes, static_cast<cudaStream_t>(stream));
+}
+int b200_eval_matches_homography(const float* keypoints0, const float* keypoints1, const long long* matches0, int B, int M,
+                                 int N, const float* H_0to1, float* out, b200_stream_t stream) {
+    return launch_eval_homography(keypoints0, keypoints1, matches0, B, M, N, H_0to1, out, static_cast<cudaStream_t>(stream));
+}
+int b200_eval_matches_epipolar(const float* keypoints0, const float* keypoints1, const long long* matches0, int B, int M,
+                               int N, const float* cam0, const float* cam1, const float* T_0to1, float* out,
+                               b200_stream_t stream) {
+    return launch_eval_epipolar(keypoints0, keypoints1, matches0, B, M, N, cam0, cam1, T_0to1, out,
+                                static_cast<cudaStream_t>(stream));
+}
+int b200_eval_homography_dlt(const float* keypoints0, const float* keypoints1, const long long* matches0,
+                             const float* mscores0, int B, int M, int N, const float* H_gt, const float* image_size,
+                             float* H_out, float* err_out, b200_stream_t stream) {
+    return launch_eval_dlt(keypoints0, keypoints1, matches0, mscores0, B, M, N, H_gt, image_size, H_out, err_out,
+                           static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -367,3 +367,91 @@ def sg_sinkhorn_assignment(cost, bin_score, iters, threshold):
                                                           _ptr(ws), _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0),
                                                           _ptr(ms1), _stream()))
     return scores, m0, m1, ms0, ms1
+
+
+# ---- rows either side of the path: pre-processing, export packing, match metrics ----------------------
+def prep_resize(src, out_hw, taps_x=None, taps_y=None, pad_hw=None, mask=False):
+    """ImagePreprocessor resize on the device.  src: float32 (B,C,H,W) in [0,1] or uint8 (B,H,W,C).
+    taps_x / taps_y: CPU float32 Gaussian taps (odd lengths) or None for no anti-alias blur.
+    Returns (image (B,C,pad_h,pad_w) float32, mask (B,pad_h,pad_w) uint8 or None)."""
+    _require_cuda(src)
+    u8 = src.dtype == torch.uint8
+    if u8:
+        b, h, w, c = src.shape
+    else:
+        if src.dtype != torch.float32:
+            raise ValueError("prep_resize: the image must be float32 (B,C,H,W) or uint8 (B,H,W,C)")
+        b, c, h, w = src.shape
+    src = src.contiguous()
+    oh, ow = int(out_hw[0]), int(out_hw[1])
+    ph, pw = (oh, ow) if pad_hw is None else (int(pad_hw[0]), int(pad_hw[1]))
+    dev = src.device
+    out = torch.empty(b, c, ph, pw, dtype=torch.float32, device=dev)
+    msk = torch.empty(b, ph, pw, dtype=torch.uint8, device=dev) if mask else None
+    blur = taps_x is not None and taps_y is not None and (len(taps_x) > 1 or len(taps_y) > 1)
+    tmp = torch.empty(b, c, h, w, dtype=torch.float32, device=dev) if blur else None
+    tx = taps_x.detach().to("cpu", torch.float32).contiguous() if blur else None
+    ty = taps_y.detach().to("cpu", torch.float32).contiguous() if blur else None
+    # algorithmic bytes: read the source once, write the result once (the blur scratch is extra traffic)
+    work = float(src.numel() * src.element_size() + out.numel() * 4)
+    with _timed("prep_resize", 2 if blur else 1, work):
+        _lib.check(_lib.lib().b200_prep_resize(
+            _ptr(src), 1 if u8 else 0, b, c, h, w, oh, ow, tx.data_ptr() if blur else None, len(tx) if blur else 1,
+            ty.data_ptr() if blur else None, len(ty) if blur else 1, _ptr(tmp), _ptr(out), ph, pw, _ptr(msk), _stream()))
+    return out, msk
+
+
+def export_pack(fields, B, record_bytes, as_half, records):
+    """fields: list of (tensor, kind, elems_per_pair, dst_offset, scales or None); records: uint8 (B, record_bytes)."""
+    arr = (_lib.ExportField * len(fields))()
+    keep = []
+    for i, (t, kind, n, off, scales) in enumerate(fields):
+        _require_cuda(t, scales)
+        t = t.contiguous()
+        keep.append(t)
+        arr[i].src, arr[i].kind, arr[i].elems_per_pair, arr[i].dst_offset = _ptr(t), kind, n, off
+        arr[i].scales = _ptr(scales)
+    with _timed("export_pack", 1, float(B * record_bytes * 2)):
+        _lib.check(_lib.lib().b200_export_pack(arr, len(fields), B, int(bool(as_half)), _ptr(records), record_bytes,
+                                               _stream()))
+
+
+def eval_matches_homography(kp0, kp1, m0, H):
+    """(B,M,2), (B,N,2), (B,M) int64, (B,3,3) -> (B,4) = prec@1px, prec@3px, num_matches, num_keypoints."""
+    _require_cuda(kp0, kp1, m0, H)
+    B, M, _ = kp0.shape
+    out = torch.empty(B, 4, dtype=torch.float32, device=kp0.device)
+    with _timed("eval_homography", 1, B * (M * 24.0)):
+        _lib.check(_lib.lib().b200_eval_matches_homography(_ptr(kp0.float().contiguous()), _ptr(kp1.float().contiguous()),
+                                                           _ptr(m0.contiguous()), B, M, kp1.shape[1],
+                                                           _ptr(H.float().reshape(B, 9).contiguous()), _ptr(out), _stream()))
+    return out
+
+
+def eval_matches_epipolar(kp0, kp1, m0, cam0, cam1, T01):
+    """cam: (B,4) = fx, fy, cx, cy; T01: (B,12) = R row-major | t -> (B,5)."""
+    _require_cuda(kp0, kp1, m0, cam0, cam1, T01)
+    B, M, _ = kp0.shape
+    out = torch.empty(B, 5, dtype=torch.float32, device=kp0.device)
+    with _timed("eval_epipolar", 1, B * (M * 24.0)):
+        _lib.check(_lib.lib().b200_eval_matches_epipolar(_ptr(kp0.float().contiguous()), _ptr(kp1.float().contiguous()),
+                                                         _ptr(m0.contiguous()), B, M, kp1.shape[1],
+                                                         _ptr(cam0.float().contiguous()), _ptr(cam1.float().contiguous()),
+                                                         _ptr(T01.float().contiguous()), _ptr(out), _stream()))
+    return out
+
+
+def eval_homography_dlt(kp0, kp1, m0, ms0, H_gt, image_size):
+    """Weighted DLT on the matched points + corner error: (H (B,3,3), error (B,))."""
+    _require_cuda(kp0, kp1, m0, ms0, H_gt, image_size)
+    B, M, _ = kp0.shape
+    dev = kp0.device
+    H = torch.empty(B, 3, 3, dtype=torch.float32, device=dev)
+    err = torch.empty(B, dtype=torch.float32, device=dev)
+    with _timed("eval_dlt", 1, B * (M * 28.0)):
+        _lib.check(_lib.lib().b200_eval_homography_dlt(_ptr(kp0.float().contiguous()), _ptr(kp1.float().contiguous()),
+                                                       _ptr(m0.contiguous()), _ptr(ms0.float().contiguous()), B, M,
+                                                       kp1.shape[1], _ptr(H_gt.float().reshape(B, 9).contiguous()),
+                                                       _ptr(image_size.float().reshape(B, 2).contiguous()), _ptr(H),
+                                                       _ptr(err), _stream()))
+    return H, err

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 6
+#define B200_ABI_VERSION 7
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -230,6 +230,56 @@ int b200_lg_prune(const float* match, const float* conf, int n0, int n1, float m
 int b200_lg_scatter_matches(const long long* m0, const long long* m1, const float* ms0, const float* ms1,
                             const int* ind /*[n0+n1]*/, int n0, int n1, long long* out_m0, long long* out_m1,
                             float* out_ms0, float* out_ms1, b200_stream_t stream);
+
+/* ---- pre-processing before the path (gluefactory/utils/image.py:12-101, datasets/image_pairs.py:59-90) -------- */
+/* ImagePreprocessor.__call__: resize (kornia.geometry.transform.resize = optional separable Gaussian anti-alias blur
+ * with reflect border, then F.interpolate bilinear, align_corners=False), zero padding to pad_h x pad_w (square_pad,
+ * :55-66) and the optional padding mask.  src_kind 0: float32 [B,C,H,W] in [0,1]; 1: uint8 [B,H,W,C] as cv2 reads
+ * it, converted like numpy_image_to_torch (:112-121, value / 255.0).  taps_x / taps_y are HOST arrays with the kx / ky
+ * (odd, <= 63) normalised Gaussian taps; kx = ky = 1 means no blur (taps may be NULL).  tmp: float32 [B,C,H,W]
+ * scratch for the horizontal pass (blur only).  out: float32 [B,C,pad_h,pad_w]; mask: uint8 [B,pad_h,pad_w] or NULL. */
+int b200_prep_resize(const void* src, int src_kind, int B, int C, int H, int W, int out_h, int out_w,
+                     const float* taps_x, int kx, const float* taps_y, int ky, float* tmp, float* out, int pad_h,
+                     int pad_w, unsigned char* mask, b200_stream_t stream);
+
+/* ---- export step after the path (gluefactory/utils/export_predictions.py:40-77) ------------------------------ */
+/* Packs a batch of predictions into fixed-size per-pair records on the device, so that ONE device-to-host copy per
+ * batch replaces the reference's `.cpu()` per tensor per pair.  A field copies elems_per_pair elements of pair b from
+ * src + b * elems_per_pair to records + b * record_bytes + dst_offset.  Kinds: F32 copy; F32_KEYPOINTS = (x, y)
+ * pairs multiplied by 1 / scales[b] (the renormalisation at :44-50; scales is a DEVICE array [B,2]); I64 copy.
+ * as_half converts the float fields to fp16 (:66-70).  `fields` is a HOST array. */
+enum { B200_EXPORT_F32 = 0, B200_EXPORT_F32_KEYPOINTS = 1, B200_EXPORT_I64 = 2 };
+#define B200_EXPORT_MAX_FIELDS 16
+typedef struct {
+    const void* src;
+    const float* scales;
+    long long elems_per_pair;
+    long long dst_offset; /* bytes inside a record; multiple of 4 (8 for I64) */
+    int kind;
+    int reserved;
+} b200_export_field;
+int b200_export_pack(const b200_export_field* fields, int num_fields, int B, int as_half, void* records,
+                     long long record_bytes, b200_stream_t stream);
+
+/* ---- match metrics on the device (gluefactory/eval/utils.py) ------------------------------------------------- */
+/* eval_matches_homography (:76-96, sym_homography_error geometry/homography.py:319-328): per pair
+ * out[b] = {prec@1px, prec@3px, num_matches, num_keypoints}.  H_0to1: float32 [B,9] row-major. */
+int b200_eval_matches_homography(const float* keypoints0 /*[B,M,2]*/, const float* keypoints1 /*[B,N,2]*/,
+                                 const long long* matches0 /*[B,M]*/, int B, int M, int N, const float* H_0to1,
+                                 float* out /*[B,4]*/, b200_stream_t stream);
+/* eval_matches_epipolar (:40-73, generalized_epi_dist essential=True, geometry/epipolar.py:32-56,75-85) for pinhole
+ * cameras: cam = (fx, fy, cx, cy) per pair, T_0to1 = R (row-major 9) | t (3).
+ * out[b] = {epi_prec@1e-4, epi_prec@5e-4, epi_prec@1e-3, num_matches, num_keypoints} (NaN precisions without matches) */
+int b200_eval_matches_epipolar(const float* keypoints0, const float* keypoints1, const long long* matches0, int B,
+                               int M, int N, const float* cam0 /*[B,4]*/, const float* cam1 /*[B,4]*/,
+                               const float* T_0to1 /*[B,12]*/, float* out /*[B,5]*/, b200_stream_t stream);
+/* eval_homography_dlt (:176-196): kornia's find_homography_dlt on the matched points weighted by the matching
+ * scores (point normalisation, A^T W A, eigenvector of the smallest eigenvalue), then homography_corner_error against
+ * H_gt (geometry/homography.py:341-347).  H_out [B,9], err_out [B]; fewer than 4 matches: inf matrix, NaN error. */
+int b200_eval_homography_dlt(const float* keypoints0, const float* keypoints1, const long long* matches0,
+                             const float* mscores0 /*[B,M]*/, int B, int M, int N, const float* H_gt /*[B,9]*/,
+                             const float* image_size /*[B,2] (w,h)*/, float* H_out, float* err_out,
+                             b200_stream_t stream);
 
 #ifdef __cplusplus
 }
