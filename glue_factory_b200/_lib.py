@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("B200GLUE_LIB") or os.path.join(_HERE, "libb200glue.so
 
 EPI_BIAS_BF16, EPI_QKV_ROTARY, EPI_LN_GELU, EPI_RESID, EPI_F32 = 0, 1, 2, 3, 4
 EPI_CONV_RELU_BN, EPI_CONV_BN_L2, EPI_CONV_BN_SOFTMAX_D2S = 5, 6, 7
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 
 class GemmDesc(C.Structure):
@@ -28,6 +28,7 @@ class GemmDesc(C.Structure):
         ("out16", C.c_void_p), ("ld16", C.c_longlong),
         ("out32", C.c_void_p), ("ld32", C.c_longlong), ("out32_batch_stride", C.c_longlong),
         ("cells_h", C.c_int), ("cells_w", C.c_int),
+        ("tile_live", C.c_void_p),
     ]
 
 
@@ -102,6 +103,16 @@ _SIGNATURES = {
     "b200_lg_assignment_static_capacity": (C.c_size_t, []),
     "b200_lg_assignment_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float,
                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_lg_adaptive_decide": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p,
+                                          C.c_void_p]),
+    "b200_lg_adaptive_prune": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float] +
+                               [C.c_void_p] * 7 + [C.c_longlong] + [C.c_void_p] * 7),
+    "b200_lg_adaptive_commit": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
+    "b200_lg_adaptive_snapshot": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 10),
+    "b200_lg_assignment_live": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                          C.c_float] + [C.c_void_p] * 7),
+    "b200_lg_adaptive_scatter": (C.c_int, [C.c_void_p] * 6 + [C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5),
     "b200_prep_resize": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                    C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
                                    C.c_void_p]),

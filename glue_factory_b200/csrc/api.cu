@@ -172,6 +172,7 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
     p.out16 = d->out16; p.ld16 = d->ld16; p.out32 = d->out32; p.ld32 = d->ld32;
     p.out32_batch_stride = d->out32_batch_stride;
     p.cells_h = d->cells_h; p.cells_w = d->cells_w;
+    p.tile_live = d->tile_live;
     B200_REQUIRE(d->batch >= 0 && d->N >= 1, "gemm: bad shape (batch=%d, N=%d)", d->batch, d->N);
     if (d->batch == 0) return 0;
 
@@ -397,6 +398,43 @@ int b200_lg_scatter_matches(const long long* m0, const long long* m1, const floa
                             float* out_ms1, b200_stream_t stream) {
     return launch_scatter_matches(m0, m1, ms0, ms1, ind, n0, n1, out_m0, out_m1, out_ms0, out_ms1,
                                   static_cast<cudaStream_t>(stream));
+}
+
+int b200_lg_adaptive_decide(const float* conf, int B, int M, int N, float threshold, float depth_conf, int layer, int* state,
+                            b200_stream_t stream) {
+    return launch_adaptive_decide(conf, B, M, N, threshold, depth_conf, layer, state, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_adaptive_prune(const float* match, const float* conf, int B, int M, int N, float match_thr, float conf_thr,
+                           int* state, int* pos_scratch, int* new_counts, const float* x_src, float* x_dst,
+                           const void* xm_src, void* xm_dst, long long ld_xm, const void* cs_src, void* cs_dst,
+                           const int* ind_src, int* ind_dst, long long* prune0, long long* prune1, b200_stream_t stream) {
+    return launch_adaptive_prune(match, conf, B, M, N, match_thr, conf_thr, state, pos_scratch, new_counts, x_src, x_dst,
+                                 xm_src, xm_dst, ld_xm, cs_src, cs_dst, ind_src, ind_dst, prune0, prune1,
+                                 static_cast<cudaStream_t>(stream));
+}
+int b200_lg_adaptive_commit(int* state, const int* new_counts, int B, int M, int N, int* lens, int* tile_live,
+                            int* hist_next, b200_stream_t stream) {
+    return launch_adaptive_commit(state, new_counts, B, M, N, lens, tile_live, hist_next, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_adaptive_snapshot(int* state, int B, int M, int N, int final_pass, const float* md, float* md_out,
+                              const float* z, float* z_out, const float* x, float* x_out, const int* ind, int* ind_out,
+                              int* final_len, b200_stream_t stream) {
+    return launch_adaptive_snapshot(state, B, M, N, final_pass, md, md_out, z, z_out, x, x_out, ind, ind_out, final_len,
+                                    static_cast<cudaStream_t>(stream));
+}
+int b200_lg_assignment_live(const float* sim, const float* z0, const float* z1, int B, int M, int N, const int* live,
+                            float filter_threshold, void* workspace, float* scores, long long* matches0,
+                            long long* matches1, float* mscores0, float* mscores1, b200_stream_t stream) {
+    B200_REQUIRE(sim && z0 && z1 && workspace && scores && matches0 && matches1 && mscores0 && mscores1,
+                 "assignment_live: null argument");
+    return launch_assignment_live(sim, z0, z1, B, M, N, live, filter_threshold, workspace, scores, matches0, matches1,
+                                  mscores0, mscores1, static_cast<cudaStream_t>(stream));
+}
+int b200_lg_adaptive_scatter(const long long* m0, const long long* m1, const float* ms0, const float* ms1, const int* ind,
+                             const int* final_len, int B, int M, int N, long long* out_m0, long long* out_m1,
+                             float* out_ms0, float* out_ms1, b200_stream_t stream) {
+    return launch_adaptive_scatter(m0, m1, ms0, ms1, ind, final_len, B, M, N, out_m0, out_m1, out_ms0, out_ms1,
+                                   static_cast<cudaStream_t>(stream));
 }
 
 int b200_prep_resize(const void* src, int src_kind, int B, int C, int H, int W, int out_h, int out_w, const float* taps_x,

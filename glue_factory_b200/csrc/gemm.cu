@@ -612,6 +612,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         GTile tc = decomp((long long)blockIdx.x);
         for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
             const int nt = tc.nt, mt = tc.mt, b = tc.b;
+            if (p.tile_live != nullptr && p.tile_live[b * m_tiles + mt] == 0) continue;
             for (int hh = 0; hh < kHalves; ++hh) {
             const int brow = b * p.b_batch_rows + (nt * kHalves + hh) * BLOCK_N;
             for (int kb = 0; kb < k_blocks; ++kb) {
@@ -648,7 +649,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         uint32_t phase = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        GTile tc = decomp((long long)blockIdx.x);
+        for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
+            if (p.tile_live != nullptr && p.tile_live[tc.b * m_tiles + tc.mt] == 0) continue;
             for (int hh = 0; hh < kHalves; ++hh) {
             mbar_wait(acc_empty + acc, acc_phase ^ 1);
             tc_fence_after();
@@ -707,6 +710,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         GTile tc = decomp((long long)blockIdx.x);
         for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x, advance(tc)) {
             const int nt = tc.nt, mt = tc.mt, b = tc.b;
+            if (p.tile_live != nullptr && p.tile_live[b * m_tiles + mt] == 0) continue;
             if constexpr (EPI == EPI_LN_GELU) {
                 // accumulator stage h holds columns [256 h, 256 h + 256) of this row tile; both stages turn over once
                 // per tile, so one phase bit serves both.  `half` is this warp's column group (0..3) here.

@@ -41,6 +41,9 @@ struct GemmParams {
     long long ld32;
     long long out32_batch_stride;
     int cells_h, cells_w;  // EPI_CONV_BN_SOFTMAX_D2S: rows are (img, cell_y, cell_x)
+    // optional DEVICE array [batch * m_tiles]: row tiles marked 0 are skipped by every role (adaptive LightGlue: tiles
+    // that hold only pruned tokens or pairs that left the layer loop)
+    const int* tile_live;
 };
 
 }  // namespace b200

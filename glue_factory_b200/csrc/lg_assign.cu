@@ -88,22 +88,26 @@ struct Top2 {  // running (max, arg-max, second largest); scanning in ascending 
 // pass 1: per-tile (max, sum exp) for rows and columns; TOP2 adds (arg-max, second largest) for the
 // nearest-neighbour matcher
 template <bool TOP2>
-__global__ void __launch_bounds__(256) assign_stats_kernel(const float* __restrict__ sim, int M, int N, AssignWs w) {
+__global__ void __launch_bounds__(256) assign_stats_kernel(const float* __restrict__ sim, int M, int N, AssignWs w,
+                                                           const int* __restrict__ live) {
     __shared__ float tile[kAHalf * kAStride];
     const int b = blockIdx.z, tm = blockIdx.y, tn = blockIdx.x;
     const int tiles_n = gridDim.x, tiles_m = gridDim.y;
+    // `live` (adaptive pruning): only the first Mb rows / Nb columns of the padded [M, N] block exist
+    const int Mb = live ? live[b] : M, Nb = live ? live[gridDim.z + b] : N;
+    if (tm * kATileM >= Mb || tn * kATileN >= Nb) return;
     const int j = tn * kATileN + threadIdx.x;
-    const bool col_ok = j < N;
+    const bool col_ok = j < Nb;
     const int rrow = threadIdx.x >> 3, seg = threadIdx.x & 7;
     const float* base = sim + (long long)b * M * N;
     float cm = -INFINITY, cs = 0.f;
     Top2 ctop;
     for (int h = 0; h < kATileM / kAHalf; ++h) {
         const int i0 = tm * kATileM + h * kAHalf;
-        if (i0 >= M) break;
+        if (i0 >= Mb) break;
         float v[kAHalf];
 #pragma unroll
-        for (int r = 0; r < kAHalf; ++r) v[r] = (col_ok && i0 + r < M) ? __ldg(base + (long long)(i0 + r) * N + j) : -INFINITY;
+        for (int r = 0; r < kAHalf; ++r) v[r] = (col_ok && i0 + r < Mb) ? __ldg(base + (long long)(i0 + r) * N + j) : -INFINITY;
         // column side
         float m = cm;
 #pragma unroll
@@ -145,7 +149,7 @@ __global__ void __launch_bounds__(256) assign_stats_kernel(const float* __restri
                 rtop.merge(ov1, oi1, ov2);
             }
         }
-        if (seg == 0 && i0 + rrow < M) {
+        if (seg == 0 && i0 + rrow < Mb) {
             const long long at = ((long long)b * M + i0 + rrow) * tiles_n + tn;
             w.row_part[at] = make_float2(rm, rs);
             if (TOP2) w.row_top[at] = make_float2(__int_as_float(rtop.i1), rtop.v2);
@@ -162,67 +166,75 @@ __global__ void __launch_bounds__(256) assign_stats_kernel(const float* __restri
 // combine the partial statistics, fold in the matchability terms, write the dustbin row / column
 __global__ void __launch_bounds__(256) assign_combine_kernel(int M, int N, int tiles_m, int tiles_n,
                                                              const float* __restrict__ z0, const float* __restrict__ z1,
-                                                             AssignWs w, float* __restrict__ scores) {
+                                                             AssignWs w, float* __restrict__ scores,
+                                                             const int* __restrict__ live) {
     const int b = blockIdx.y;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     float* sc = scores + (long long)b * (M + 1) * (N + 1);
-    if (t < M) {
+    // with `live` the dustbin column / row sit right behind the live block (indices Nb / Mb of the padded matrix),
+    // so that scores[b, :Mb+1, :Nb+1] is the reference's (Mb+1) x (Nb+1) result
+    const int Mb = live ? live[b] : M, Nb = live ? live[gridDim.y + b] : N;
+    const int tn_live = (Nb + kATileN - 1) / kATileN, tm_live = (Mb + kATileM - 1) / kATileM;
+    if (t < Mb) {
         const float2* p = w.row_part + ((long long)b * M + t) * tiles_n;
         float m = -INFINITY;
-        for (int q = 0; q < tiles_n; ++q) m = fmaxf(m, p[q].x);
+        for (int q = 0; q < tn_live; ++q) m = fmaxf(m, p[q].x);
         float s = 0.f;
-        for (int q = 0; q < tiles_n; ++q) s += p[q].y * expf(p[q].x - m);
+        for (int q = 0; q < tn_live; ++q) s += p[q].y * expf(p[q].x - m);
         const float z = z0[(long long)b * M + t];
         w.rowterm[(long long)b * M + t] = log_sigmoid(z) - (m + logf(s));
-        sc[(long long)t * (N + 1) + N] = log_sigmoid(-z);
-    } else if (t < M + N) {
+        sc[(long long)t * (N + 1) + Nb] = log_sigmoid(-z);
+    } else if (t >= M && t < M + Nb) {
         const int j = t - M;
         float m = -INFINITY;
-        for (int q = 0; q < tiles_m; ++q) m = fmaxf(m, w.col_part[((long long)b * tiles_m + q) * N + j].x);
+        for (int q = 0; q < tm_live; ++q) m = fmaxf(m, w.col_part[((long long)b * tiles_m + q) * N + j].x);
         float s = 0.f;
-        for (int q = 0; q < tiles_m; ++q) {
+        for (int q = 0; q < tm_live; ++q) {
             const float2 v = w.col_part[((long long)b * tiles_m + q) * N + j];
             s += v.y * expf(v.x - m);
         }
         const float z = z1[(long long)b * N + j];
         w.colterm[(long long)b * N + j] = log_sigmoid(z) - (m + logf(s));
-        sc[(long long)M * (N + 1) + j] = log_sigmoid(-z);
+        sc[(long long)Mb * (N + 1) + j] = log_sigmoid(-z);
     } else if (t == M + N) {
-        sc[(long long)M * (N + 1) + N] = 0.f;
+        sc[(long long)Mb * (N + 1) + Nb] = 0.f;
     }
 }
 
 // pass 2: write the scores; ARGMAX also tracks per-tile row / column maxima (lowest index wins ties)
 template <bool ARGMAX>
 __global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __restrict__ sim, float simw, int M, int N,
-                                                              AssignWs w, float* __restrict__ scores) {
+                                                              AssignWs w, float* __restrict__ scores,
+                                                              const int* __restrict__ live) {
     __shared__ float tile[ARGMAX ? kAHalf * kAStride : 1];
     __shared__ float srt[kATileM];
     const int b = blockIdx.z, tm = blockIdx.y, tn = blockIdx.x;
     const int tiles_n = gridDim.x, tiles_m = gridDim.y;
+    const int Mb = live ? live[b] : M, Nb = live ? live[gridDim.z + b] : N;
+    if (tm * kATileM >= Mb || tn * kATileN >= Nb) return;
     const int j = tn * kATileN + threadIdx.x;
-    const bool col_ok = j < N;
+    const bool col_ok = j < Nb;
     const int rrow = threadIdx.x >> 3, seg = threadIdx.x & 7;
     const float* base = sim + (long long)b * M * N;
     float* sc = scores + (long long)b * (M + 1) * (N + 1);
     const float ct = col_ok ? w.colterm[(long long)b * N + j] : 0.f;
     if (threadIdx.x < kATileM) {
         const int i = tm * kATileM + threadIdx.x;
-        srt[threadIdx.x] = i < M ? w.rowterm[(long long)b * M + i] : 0.f;
+        srt[threadIdx.x] = i < Mb ? w.rowterm[(long long)b * M + i] : 0.f;
     }
     __syncthreads();
     float cbest = -INFINITY;
     int cidx = 0;
     for (int h = 0; h < kATileM / kAHalf; ++h) {
         const int i0 = tm * kATileM + h * kAHalf;
-        if (i0 >= M) break;
+        if (i0 >= Mb) break;
         float v[kAHalf];
 #pragma unroll
-        for (int r = 0; r < kAHalf; ++r) v[r] = (col_ok && i0 + r < M) ? __ldg(base + (long long)(i0 + r) * N + j) : -INFINITY;
+        for (int r = 0; r < kAHalf; ++r) v[r] = (col_ok && i0 + r < Mb) ? __ldg(base + (long long)(i0 + r) * N + j) : -INFINITY;
 #pragma unroll
         for (int r = 0; r < kAHalf; ++r) {
             v[r] = fmaf(simw, v[r], srt[h * kAHalf + r] + ct);  // -inf stays -inf outside the matrix
-            if (col_ok && i0 + r < M) sc[(long long)(i0 + r) * (N + 1) + j] = v[r];
+            if (col_ok && i0 + r < Mb) sc[(long long)(i0 + r) * (N + 1) + j] = v[r];
             if (ARGMAX) {
                 cidx = v[r] > cbest ? i0 + r : cidx;
                 cbest = fmaxf(cbest, v[r]);
@@ -246,7 +258,7 @@ __global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __res
                 const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
                 if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
             }
-            if (seg == 0 && i0 + rrow < M)
+            if (seg == 0 && i0 + rrow < Mb)
                 w.row_part[((long long)b * M + i0 + rrow) * tiles_n + tn] = make_float2(bv, __int_as_float(bi));
             __syncthreads();
         }
@@ -254,20 +266,23 @@ __global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __res
     if (ARGMAX && col_ok) w.col_part[((long long)b * tiles_m + tm) * N + j] = make_float2(cbest, __int_as_float(cidx));
 }
 
-__global__ void __launch_bounds__(256) assign_argmax_kernel(int M, int N, int tiles_m, int tiles_n, AssignWs w) {
+__global__ void __launch_bounds__(256) assign_argmax_kernel(int M, int N, int tiles_m, int tiles_n, AssignWs w,
+                                                            const int* __restrict__ live) {
     const int b = blockIdx.y;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < M) {
+    const int Mb = live ? live[b] : M, Nb = live ? live[gridDim.y + b] : N;
+    const int tn_live = (Nb + kATileN - 1) / kATileN, tm_live = (Mb + kATileM - 1) / kATileM;
+    if (t < Mb) {
         const float2* p = w.row_part + ((long long)b * M + t) * tiles_n;
         float2 best = p[0];
-        for (int q = 1; q < tiles_n; ++q)
+        for (int q = 1; q < tn_live; ++q)
             if (p[q].x > best.x) best = p[q];
         w.max0[(long long)b * M + t] = best.x;
         w.arg0[(long long)b * M + t] = __float_as_int(best.y);
-    } else if (t < M + N) {
+    } else if (t >= M && t < M + Nb) {
         const int j = t - M;
         float2 best = w.col_part[((long long)b * tiles_m) * N + j];
-        for (int q = 1; q < tiles_m; ++q) {
+        for (int q = 1; q < tm_live; ++q) {
             const float2 v = w.col_part[((long long)b * tiles_m + q) * N + j];
             if (v.x > best.x) best = v;
         }
@@ -278,12 +293,19 @@ __global__ void __launch_bounds__(256) assign_argmax_kernel(int M, int N, int ti
 // mutual nearest neighbours + threshold (lightglue.py:287-303); int64 matches, -1 = unmatched
 __global__ void __launch_bounds__(256) filter_matches_kernel(int M, int N, float th, AssignWs w,
                                                              long long* __restrict__ m0, long long* __restrict__ m1,
-                                                             float* __restrict__ ms0, float* __restrict__ ms1) {
+                                                             float* __restrict__ ms0, float* __restrict__ ms1,
+                                                             const int* __restrict__ live) {
     const int b = blockIdx.y;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int* a0 = w.arg0 + (long long)b * M;
     const int* a1 = w.arg1 + (long long)b * N;
     const float* mx = w.max0 + (long long)b * M;
+    const int Mb = live ? live[b] : M, Nb = live ? live[gridDim.y + b] : N;
+    if ((t < M && t >= Mb) || (t >= M && t < M + N && t - M >= Nb)) {  // padding behind the live block
+        if (t < M) { m0[(long long)b * M + t] = -1; ms0[(long long)b * M + t] = 0.f; }
+        else { m1[(long long)b * N + t - M] = -1; ms1[(long long)b * N + t - M] = 0.f; }
+        return;
+    }
     if (t < M) {
         const int j = a0[t];
         const bool mutual = a1[j] == t;
@@ -303,27 +325,35 @@ __global__ void __launch_bounds__(256) filter_matches_kernel(int M, int N, float
 int launch_assignment(const float* sim, const float* z0, const float* z1, int B, int M, int N, float threshold,
                       void* workspace, float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
                       cudaStream_t stream) {
+    return launch_assignment_live(sim, z0, z1, B, M, N, nullptr, threshold, workspace, scores, m0, m1, ms0, ms1, stream);
+}
+
+// same on padded [B, M, N] problems whose live sizes (Mb, Nb) are DEVICE values live[b], live[B + b] (adaptive
+// pruning without host synchronisation); live == nullptr: every pair is M x N
+int launch_assignment_live(const float* sim, const float* z0, const float* z1, int B, int M, int N, const int* live,
+                           float threshold, void* workspace, float* scores, long long* m0, long long* m1, float* ms0,
+                           float* ms1, cudaStream_t stream) {
     B200_REQUIRE(M >= 1 && N >= 1, "assignment: needs at least one keypoint per image (M=%d, N=%d)", M, N);
     if (B == 0) return 0;
     const AssignWs w = carve(workspace, B, M, N);
     const int tn = (N + kATileN - 1) / kATileN, tm = (M + kATileM - 1) / kATileM;
     dim3 tiles(tn, tm, B), lin((M + N + 1 + 255) / 256, B);
-    assign_stats_kernel<false><<<tiles, 256, 0, stream>>>(sim, M, N, w);
-    assign_combine_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, z0, z1, w, scores);
+    assign_stats_kernel<false><<<tiles, 256, 0, stream>>>(sim, M, N, w, live);
+    assign_combine_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, z0, z1, w, scores, live);
     B200_CHECK_CUDA(cudaGetLastError());
-    return launch_assignment_finalize(sim, 2.0f, B, M, N, threshold, workspace, scores, m0, m1, ms0, ms1, stream);
+    return launch_assignment_finalize(sim, 2.0f, B, M, N, threshold, workspace, scores, m0, m1, ms0, ms1, stream, live);
 }
 
 // scores[:M,:N] = simw * sim + rowterm + colterm (terms in the workspace), then arg-max + mutual-NN filter
 int launch_assignment_finalize(const float* sim, float simw, int B, int M, int N, float threshold, void* workspace,
                                float* scores, long long* m0, long long* m1, float* ms0, float* ms1,
-                               cudaStream_t stream) {
+                               cudaStream_t stream, const int* live) {
     const AssignWs w = carve(workspace, B, M, N);
     const int tn = (N + kATileN - 1) / kATileN, tm = (M + kATileM - 1) / kATileM;
     dim3 tiles(tn, tm, B), lin((M + N + 1 + 255) / 256, B);
-    assign_finalize_kernel<true><<<tiles, 256, 0, stream>>>(sim, simw, M, N, w, scores);
-    assign_argmax_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, w);
-    filter_matches_kernel<<<lin, 256, 0, stream>>>(M, N, threshold, w, m0, m1, ms0, ms1);
+    assign_finalize_kernel<true><<<tiles, 256, 0, stream>>>(sim, simw, M, N, w, scores, live);
+    assign_argmax_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, w, live);
+    filter_matches_kernel<<<lin, 256, 0, stream>>>(M, N, threshold, w, m0, m1, ms0, ms1, live);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
 }
@@ -459,9 +489,9 @@ int launch_nn_match(const float* sim, int B, int M, int N, float ratio_sq, float
     const AssignWs w = carve(workspace, B, M, N, true);
     const int tn = (N + kATileN - 1) / kATileN, tm = (M + kATileM - 1) / kATileM;
     dim3 tiles(tn, tm, B), lin((M + N + 1 + 255) / 256, B);
-    assign_stats_kernel<true><<<tiles, 256, 0, stream>>>(sim, M, N, w);
+    assign_stats_kernel<true><<<tiles, 256, 0, stream>>>(sim, M, N, w, nullptr);
     nn_combine_kernel<<<lin, 256, 0, stream>>>(M, N, tm, tn, ratio_sq, dist_sq, w, scores);
-    assign_finalize_kernel<false><<<tiles, 256, 0, stream>>>(sim, 2.0f, M, N, w, scores);
+    assign_finalize_kernel<false><<<tiles, 256, 0, stream>>>(sim, 2.0f, M, N, w, scores, nullptr);
     nn_mutual_kernel<<<lin, 256, 0, stream>>>(M, N, mutual, w, m0, m1, ms0, ms1);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

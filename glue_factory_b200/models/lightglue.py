@@ -207,31 +207,60 @@ class LightGlue(nn.Module):
 
     # -- building blocks ---------------------------------------------------------------------------
     @staticmethod
-    def _ffn_block(ws, T, w1, b1, g, be, eps, w2, b2):
+    def _ffn_block(ws, T, w1, b1, g, be, eps, w2, b2, tile_live=None):
         ops.gemm(ws["xm"], w1, M=T, N=512, K=512, lda=512, block_n=512, epilogue=ops.EPI_LN_GELU, bias=b1,
-                 ln_gamma=g, ln_beta=be, ln_eps=eps, out16=ws["h"], ld16=512)
+                 ln_gamma=g, ln_beta=be, ln_eps=eps, out16=ws["h"], ld16=512, tile_live=tile_live)
         ops.gemm(ws["h"], w2, M=T, N=256, K=512, lda=512, block_n=256, epilogue=ops.EPI_RESID, bias=b2,
-                 resid=ws["x32"], out32=ws["x32"], ld32=256, out16=ws["xm"], ld16=512)
+                 resid=ws["x32"], out32=ws["x32"], ld32=256, out16=ws["xm"], ld16=512, tile_live=tile_live)
 
-    def _layer(self, P, ws, T, seqs_self, seqs_cross, nseq, max_len, work_self=0.0, work_cross=0.0):
+    def _layer(self, P, ws, T, seqs_self, seqs_cross, nseq, max_len, work_self=0.0, work_cross=0.0, lens=None,
+               tile_live=None):
+        """One TransformerLayer (lightglue.py:218-247).  `lens` / `tile_live` (adaptive mode): device-side live
+        sequence lengths for the attention kernels and live 128-row tiles for the GEMMs."""
+        tl = tile_live
         # self attention (lightglue.py:144-157)
         ops.gemm(ws["xm"], P["wqkv"], M=T, N=768, K=256, lda=512, block_n=256, epilogue=ops.EPI_QKV_ROTARY,
-                 bias=P["bqkv"], cossin=ws["cs"], rot_cols=512, out16=ws["qkv"], ld16=768)
+                 bias=P["bqkv"], cossin=ws["cs"], rot_cols=512, out16=ws["qkv"], ld16=768, tile_live=tl)
         ops.attention(ws["qkv"], ws["qkv"], ws["qkv"], seqs_self, num_seqs=nseq, max_q_len=max_len, heads=4,
                       ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=ws["ctx"],
-                      ld_out=256, attn_work=work_self)
+                      ld_out=256, attn_work=work_self, len_override=lens)
         ops.gemm(ws["ctx"], P["wo"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
-                 bias=P["bo"], out16=ws["xm"], out16_col0=256, ld16=512)
-        self._ffn_block(ws, T, P["s_w1"], P["s_b1"], P["s_g"], P["s_be"], P["s_eps"], P["s_w2"], P["s_b2"])
+                 bias=P["bo"], out16=ws["xm"], out16_col0=256, ld16=512, tile_live=tl)
+        self._ffn_block(ws, T, P["s_w1"], P["s_b1"], P["s_g"], P["s_be"], P["s_eps"], P["s_w2"], P["s_b2"], tl)
         # bidirectional cross attention (lightglue.py:186-215)
         ops.gemm(ws["xm"], P["wc"], M=T, N=512, K=256, lda=512, block_n=256, epilogue=ops.EPI_BIAS_BF16,
-                 bias=P["bc"], out16=ws["qkv"], ld16=768)
+                 bias=P["bc"], out16=ws["qkv"], ld16=768, tile_live=tl)
         ops.attention(ws["qkv"], ws["qkv"], ws["qkv"], seqs_cross, num_seqs=nseq, max_q_len=max_len, heads=4,
                       ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=0, v_col0=256, scale=0.125, out=ws["ctx"],
-                      ld_out=256, attn_work=work_cross)
+                      ld_out=256, attn_work=work_cross, len_override=lens)
         ops.gemm(ws["ctx"], P["wco"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
-                 bias=P["bco"], out16=ws["xm"], out16_col0=256, ld16=512)
-        self._ffn_block(ws, T, P["c_w1"], P["c_b1"], P["c_g"], P["c_be"], P["c_eps"], P["c_w2"], P["c_b2"])
+                 bias=P["bco"], out16=ws["xm"], out16_col0=256, ld16=512, tile_live=tl)
+        self._ffn_block(ws, T, P["c_w1"], P["c_b1"], P["c_g"], P["c_be"], P["c_eps"], P["c_w2"], P["c_b2"], tl)
+
+    def _project(self, A, ws, T, tile_live=None):
+        """final_proj (fp32-grade two-term split GEMM, scaled by dim^-1/4) and matchability logits of every row:
+        (md32 [T,256], z [T])  (lightglue.py:270-275,283-284)"""
+        dev = ws["x32"].device
+        z = torch.empty(T, dtype=torch.float32, device=dev)
+        ops.lg_rowdot(ws["x32"], T, A["wm"], A["bm"], z)
+        xs = torch.empty(T, 768, dtype=torch.bfloat16, device=dev)
+        ops.split_hilo(ws["x32"], T, 256, T, xs)
+        md32 = torch.empty(T, 256, dtype=torch.float32, device=dev)
+        ops.gemm(xs, A["wf_split"], M=T, N=256, K=768, lda=768, block_n=256, epilogue=ops.EPI_F32, bias=A["bf"],
+                 alpha=1.0, out32=md32, ld32=256, out32_batch_stride=0, tile_live=tile_live)
+        return md32, z
+
+    @staticmethod
+    def _similarity(md32, B, M, N, T):
+        """sim[b] = md0_b . md1_b^T through the two-term split (K = 768), fp32 [B,M,N] (lightglue.py:276)"""
+        dev = md32.device
+        md = torch.empty(T, 768, dtype=torch.bfloat16, device=dev)
+        ops.split_hilo(md32, T, 256, B * M, md)
+        sim = torch.empty(B, M, N, dtype=torch.float32, device=dev)
+        ops.gemm(md, md, M=M, N=N, K=768, lda=768, ldb=768, a_rows=T, b_row0=B * M, b_rows=B * N, batch=B,
+                 a_batch_rows=M, b_batch_rows=N, block_n=256 if N > 128 else 128, epilogue=ops.EPI_F32, alpha=1.0,
+                 out32=sim, ld32=N, out32_batch_stride=M * N)
+        return sim
 
     def _assign(self, A, ws, B, M, N, T):
         """MatchAssignment.forward + filter_matches on the current descriptors (lightglue.py:265-303).
@@ -240,27 +269,19 @@ class LightGlue(nn.Module):
         similarity therefore run as two-term bf16 split GEMMs (K = 3 x 256: hi.hi + hi.lo + lo.hi, fp32
         accumulate) on the fp32 residual stream, i.e. with ~2^-16 relative operand error instead of 2^-9."""
         dev = ws["x32"].device
-        z = torch.empty(T, dtype=torch.float32, device=dev)
-        ops.lg_rowdot(ws["x32"], T, A["wm"], A["bm"], z)
-        sim = torch.empty(B, M, N, dtype=torch.float32, device=dev)
-        bn = 256 if N > 128 else 128
         if ASSIGN_BF16:
+            z = torch.empty(T, dtype=torch.float32, device=dev)
+            ops.lg_rowdot(ws["x32"], T, A["wm"], A["bm"], z)
+            sim = torch.empty(B, M, N, dtype=torch.float32, device=dev)
+            bn = 256 if N > 128 else 128
             ops.gemm(ws["xm"], A["wf"], M=T, N=256, K=256, lda=512, block_n=256, epilogue=ops.EPI_BIAS_BF16,
                      bias=A["bf"], out16=ws["md"], ld16=256)
             ops.gemm(ws["md"], ws["md"], M=M, N=N, K=256, lda=256, ldb=256, a_rows=T, b_row0=B * M, b_rows=B * N,
                      batch=B, a_batch_rows=M, b_batch_rows=N, block_n=bn, epilogue=ops.EPI_F32,
                      alpha=1.0, out32=sim, ld32=N, out32_batch_stride=M * N)
         else:
-            xs = torch.empty(T, 768, dtype=torch.bfloat16, device=dev)
-            ops.split_hilo(ws["x32"], T, 256, T, xs)
-            md32 = torch.empty(T, 256, dtype=torch.float32, device=dev)
-            ops.gemm(xs, A["wf_split"], M=T, N=256, K=768, lda=768, block_n=256, epilogue=ops.EPI_F32, bias=A["bf"],
-                     alpha=1.0, out32=md32, ld32=256, out32_batch_stride=0)
-            md = torch.empty(T, 768, dtype=torch.bfloat16, device=dev)
-            ops.split_hilo(md32, T, 256, B * M, md)
-            ops.gemm(md, md, M=M, N=N, K=768, lda=768, ldb=768, a_rows=T, b_row0=B * M, b_rows=B * N, batch=B,
-                     a_batch_rows=M, b_batch_rows=N, block_n=bn, epilogue=ops.EPI_F32, alpha=1.0, out32=sim,
-                     ld32=N, out32_batch_stride=M * N)
+            md32, z = self._project(A, ws, T)
+            sim = self._similarity(md32, B, M, N, T)
         return ops.lg_assignment(sim, z[: B * M], z[B * M:], self.conf.filter_threshold) + (sim,)
 
     def assign_from_descriptors(self, desc0, desc1, layer=None):
@@ -278,16 +299,19 @@ class LightGlue(nn.Module):
             layer = self.conf.n_layers - 1 if layer is None else layer
             return self._assign(P["assign"][layer], ws, B, M, N, T)[:5]
 
-    def _workspace(self, T, dev):
+    def _workspace(self, T, dev, zero=False):
+        """`zero`: adaptive mode keeps dead rows in the buffers (pruned tokens, skipped tiles); they must hold finite
+        values because the attention kernel multiplies masked keys' V rows by exact zeros."""
         bf = torch.bfloat16
+        new = torch.zeros if zero else torch.empty
         return dict(
-            x32=torch.empty(T, 256, dtype=torch.float32, device=dev),
-            xm=torch.empty(T, 512, dtype=bf, device=dev),
-            qkv=torch.empty(T, 768, dtype=bf, device=dev),
-            ctx=torch.empty(T, 256, dtype=bf, device=dev),
-            h=torch.empty(T, 512, dtype=bf, device=dev),
-            md=torch.empty(T, 256, dtype=bf, device=dev),
-            cs=torch.empty(T, 32, 2, dtype=torch.float32, device=dev),
+            x32=new(T, 256, dtype=torch.float32, device=dev),
+            xm=new(T, 512, dtype=bf, device=dev),
+            qkv=new(T, 768, dtype=bf, device=dev),
+            ctx=new(T, 256, dtype=bf, device=dev),
+            h=new(T, 512, dtype=bf, device=dev),
+            md=new(T, 256, dtype=bf, device=dev),
+            cs=new(T, 32, 2, dtype=torch.float32, device=dev),
         )
 
     def forward(self, data: dict) -> dict:

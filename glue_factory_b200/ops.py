@@ -107,7 +107,7 @@ def gemm(a, w, *, M, N, K, lda, block_n, epilogue, a_rows=None, a_col0=0, ldb=No
          a_batch_rows=0, b_batch_rows=0, b_row0=0, b_rows=None, conv=None, bias=None, scale=None, shift=None,
          relu=0, pool=0, alpha=1.0, resid=None, cossin=None, rot_cols=0, ln_gamma=None, ln_beta=None,
          ln_eps=1e-5, out16=None, out16_col0=0, ld16=0, out32=None, ld32=0, out32_batch_stride=0,
-         cells=(0, 0)):
+         cells=(0, 0), tile_live=None):
     """C = epilogue(A . W^T) on the tcgen05 path.  `a`/`w` are bf16 tensors; views are expressed with
     (a_col0, lda) / (b_row0, ldb) so that a column slice of a wider matrix can be an operand."""
     _require_cuda(a, w, out16, out32)
@@ -131,6 +131,7 @@ def gemm(a, w, *, M, N, K, lda, block_n, epilogue, a_rows=None, a_col0=0, ldb=No
     d.out16, d.ld16 = _ptr(out16, out16_col0), ld16
     d.out32, d.ld32, d.out32_batch_stride = _ptr(out32), ld32, out32_batch_stride
     d.cells_h, d.cells_w = cells
+    d.tile_live = _ptr(tile_live)
     if conv is not None:
         tag, work = f"conv3x3_{conv[2]}to{N}", 2.0 * batch * conv[0] * conv[1] * N * K
     else:
@@ -455,3 +456,56 @@ def eval_homography_dlt(kp0, kp1, m0, ms0, H_gt, image_size):
                                                        _ptr(image_size.float().reshape(B, 2).contiguous()), _ptr(H),
                                                        _ptr(err), _stream()))
     return H, err
+
+
+# ---- adaptive depth / width for a batch of pairs (state on the device) ------------------------------------
+def lg_adaptive_decide(conf, B, M, N, threshold, depth_conf, layer, state):
+    with _timed("lg_adaptive_decide", 1, B * (M + N) * 4.0):
+        _lib.check(_lib.lib().b200_lg_adaptive_decide(_ptr(conf), B, M, N, float(threshold), float(depth_conf), int(layer),
+                                                      _ptr(state), _stream()))
+
+
+def lg_adaptive_prune(match, conf, B, M, N, match_thr, conf_thr, state, pos, newc, src, dst, ind_src, ind_dst, prune0,
+                      prune1):
+    with _timed("lg_adaptive_prune", 2, B * (M + N) * 3600.0):
+        _lib.check(_lib.lib().b200_lg_adaptive_prune(
+            _ptr(match), _ptr(conf), B, M, N, float(match_thr), float(conf_thr), _ptr(state), _ptr(pos), _ptr(newc),
+            _ptr(src["x32"]), _ptr(dst["x32"]), _ptr(src["xm"]), _ptr(dst["xm"]), 512, _ptr(src["cs"]), _ptr(dst["cs"]),
+            _ptr(ind_src), _ptr(ind_dst), _ptr(prune0), _ptr(prune1), _stream()))
+
+
+def lg_adaptive_commit(state, newc, B, M, N, lens, tile_live, hist_next=None):
+    with _timed("lg_adaptive_commit", 2 if newc is not None else 1, 0.0):
+        _lib.check(_lib.lib().b200_lg_adaptive_commit(_ptr(state), _ptr(newc), B, M, N, _ptr(lens), _ptr(tile_live),
+                                                      _ptr(hist_next), _stream()))
+
+
+def lg_adaptive_snapshot(state, B, M, N, final_pass, md, md_out, z, z_out, x, x_out, ind, ind_out, final_len):
+    with _timed("lg_adaptive_snapshot", 1 if final_pass else 2, B * (M + N) * 4100.0):
+        _lib.check(_lib.lib().b200_lg_adaptive_snapshot(_ptr(state), B, M, N, int(final_pass), _ptr(md), _ptr(md_out),
+                                                        _ptr(z), _ptr(z_out), _ptr(x), _ptr(x_out), _ptr(ind),
+                                                        _ptr(ind_out), _ptr(final_len), _stream()))
+
+
+def lg_assignment_live(sim, z0, z1, live, threshold):
+    """lg_assignment on padded problems with device-side live sizes; scores is zero-filled outside the live blocks."""
+    b, m, n = sim.shape
+    dev = sim.device
+    ws = torch.empty(_lib.lib().b200_lg_assignment_workspace(b, m, n), dtype=torch.uint8, device=dev)
+    scores = torch.zeros(b, m + 1, n + 1, dtype=torch.float32, device=dev)
+    m0 = torch.empty(b, m, dtype=torch.int64, device=dev)
+    m1 = torch.empty(b, n, dtype=torch.int64, device=dev)
+    ms0 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    ms1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    with _timed("lg_assignment", 5, 12.0 * b * m * n):
+        _lib.check(_lib.lib().b200_lg_assignment_live(_ptr(sim), _ptr(z0), _ptr(z1), b, m, n, _ptr(live), float(threshold),
+                                                      _ptr(ws), _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1),
+                                                      _stream()))
+    return scores, m0, m1, ms0, ms1
+
+
+def lg_adaptive_scatter(m0, m1, ms0, ms1, ind, final_len, B, M, N, out_m0, out_m1, out_ms0, out_ms1):
+    with _timed("lg_scatter_matches", 1, B * (M + N) * 40.0):
+        _lib.check(_lib.lib().b200_lg_adaptive_scatter(_ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ind), _ptr(final_len),
+                                                       B, M, N, _ptr(out_m0), _ptr(out_m1), _ptr(out_ms0), _ptr(out_ms1),
+                                                       _stream()))

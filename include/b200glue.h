@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 7
+#define B200_ABI_VERSION 8
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -73,6 +73,8 @@ typedef struct {
     long long ld32;
     long long out32_batch_stride;
     int cells_h, cells_w;   /* D2S epilogue: rows are (image, cell_y, cell_x)                          */
+    const int* tile_live;   /* optional DEVICE array [batch * ceil(M/128)]: 128-row tiles marked 0 are skipped
+                               (adaptive LightGlue: pruned tokens, pairs that left the layer loop); NULL = all */
 } b200_gemm_desc;
 
 /* nn.Linear / nn.Conv2d / einsum on the path -> tcgen05 GEMM (dense path). */
@@ -230,6 +232,43 @@ int b200_lg_prune(const float* match, const float* conf, int n0, int n1, float m
 int b200_lg_scatter_matches(const long long* m0, const long long* m1, const float* ms0, const float* ms1,
                             const int* ind /*[n0+n1]*/, int n0, int n1, long long* out_m0, long long* out_m1,
                             float* out_ms0, float* out_ms1, b200_stream_t stream);
+
+/* ---- adaptive depth / width for a BATCH of pairs, no host synchronisation (lightglue.py:470-511,527-552) -------
+ * Token rows: image 0 of pair b = [b M, b M + M), image 1 = [B M + b N, ...); the live tokens of a segment are its
+ * first m_b / n_b rows.  state: int32 [5 B] = m | n | active | exit_layer | just_exited (caller initialises
+ * m = M, n = N, active = 1, exit_layer = n_layers - 1, just_exited = 0). */
+/* check_if_stop (:541-552) per active pair on conf = sigmoid(token confidence) of every row: a pair whose ratio
+ * 1 - below / (M + N) exceeds depth_conf gets active = 0, exit_layer = layer, just_exited = 1 */
+int b200_lg_adaptive_decide(const float* conf, int B, int M, int N, float threshold, float depth_conf, int layer,
+                            int* state, b200_stream_t stream);
+/* get_pruning_mask (:532-539) + ordered compaction inside every active pair's segments (src -> dst buffers, as
+ * b200_lg_prune), prune counters [B,M] / [B,N] += 1 for kept keypoints; new lengths go to new_counts [2 B]
+ * (committed by b200_lg_adaptive_commit).  conf may be NULL (no depth confidence). */
+int b200_lg_adaptive_prune(const float* match, const float* conf, int B, int M, int N, float match_thr, float conf_thr,
+                           int* state, int* pos_scratch /*[B (M+N)]*/, int* new_counts, const float* x_src, float* x_dst,
+                           const void* xm_src, void* xm_dst, long long ld_xm, const void* cs_src, void* cs_dst,
+                           const int* ind_src, int* ind_dst, long long* prune0, long long* prune1, b200_stream_t stream);
+/* commit new_counts (NULL: keep the lengths) and refresh lens [2 B] (live lengths, 0 for inactive pairs: the
+ * len_override of b200_attention), tile_live [ceil(B (M+N) / 128)] (b200_gemm_desc.tile_live) and, if not NULL,
+ * hist_next [2 B] (lengths entering the next layer, for the executed-FLOPs report) */
+int b200_lg_adaptive_commit(int* state, const int* new_counts, int B, int M, int N, int* lens, int* tile_live,
+                            int* hist_next, b200_stream_t stream);
+/* keep what the final assignment needs of the pairs that just left the loop (final_pass = 0; clears just_exited) or
+ * that are still active after the last layer (final_pass = 1): projected descriptors md, matchability logits z,
+ * residual stream x, index map ind -> *_out (same row layout), live lengths -> final_len [2 B] */
+int b200_lg_adaptive_snapshot(int* state, int B, int M, int N, int final_pass, const float* md, float* md_out,
+                              const float* z, float* z_out, const float* x, float* x_out, const int* ind, int* ind_out,
+                              int* final_len, b200_stream_t stream);
+/* b200_lg_assignment on padded [B,M,N] problems with DEVICE live sizes live[b] x live[B+b]; the dustbin column / row
+ * are written at indices live[B+b] / live[b], so scores[b, :m+1, :n+1] is the reference result; matches beyond
+ * the live block are -1 / 0.  The caller zero-fills `scores`. */
+int b200_lg_assignment_live(const float* sim, const float* z0, const float* z1, int B, int M, int N, const int* live,
+                            float filter_threshold, void* workspace, float* scores, long long* matches0,
+                            long long* matches1, float* mscores0, float* mscores1, b200_stream_t stream);
+/* b200_lg_scatter_matches for every pair at once (index map and lengths as snapshot left them) */
+int b200_lg_adaptive_scatter(const long long* m0, const long long* m1, const float* ms0, const float* ms1,
+                             const int* ind, const int* final_len, int B, int M, int N, long long* out_m0,
+                             long long* out_m1, float* out_ms0, float* out_ms1, b200_stream_t stream);
 
 /* ---- pre-processing before the path (gluefactory/utils/image.py:12-101, datasets/image_pairs.py:59-90) -------- */
 /* ImagePreprocessor.__call__: resize (kornia.geometry.transform.resize = optional separable Gaussian anti-alias blur
