@@ -257,12 +257,20 @@ int b200_attention(const b200_attn_desc* d, b200_stream_t stream_) {
     return launch_attention(tq, tk, tv, p, d->num_seqs, d->max_q_len, d->heads, num_sms, stream);
 }
 
+static int conv1a_any(const void* image, int u8, int B, int C, int H, int W, const float* w, const float* bias,
+                      const float* scale, const float* shift, void* out_nhwc, b200_stream_t stream) {
+    return launch_conv1a(image, u8, B, C, H, W, w, bias, scale, shift, out_nhwc, static_cast<cudaStream_t>(stream));
+}
 int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* w, const float* bias,
                    const float* scale, const float* shift, void* out_nhwc, b200_stream_t stream) {
-    return launch_conv1a(image, B, C, H, W, w, bias, scale, shift, out_nhwc, static_cast<cudaStream_t>(stream));
+    return conv1a_any(image, 0, B, C, H, W, w, bias, scale, shift, out_nhwc, stream);
 }
-int b200_sp_conv_stem(const float* image, int B, int C, int H, int W, const float* w1, const float* host_params,
-                      const void* w2, int pool, void* out_nhwc, b200_stream_t stream) {
+int b200_sp_conv1a_u8(const unsigned char* image, int B, int C, int H, int W, const float* w, const float* bias,
+                      const float* scale, const float* shift, void* out_nhwc, b200_stream_t stream) {
+    return conv1a_any(image, 1, B, C, H, W, w, bias, scale, shift, out_nhwc, stream);
+}
+static int conv_stem_any(const void* image, int u8, int B, int C, int H, int W, const float* w1, const float* host_params,
+                         const void* w2, int pool, void* out_nhwc, b200_stream_t stream) {
     B200_REQUIRE(image && w1 && host_params && w2 && out_nhwc, "conv_stem: null argument");
     B200_REQUIRE(C == 1 || C == 3, "conv_stem: image must have 1 or 3 channels, got %d", C);
     B200_REQUIRE(B >= 0 && H > 0 && W > 0, "conv_stem: bad sizes");
@@ -279,13 +287,21 @@ int b200_sp_conv_stem(const float* image, int B, int C, int H, int W, const floa
     CUtensorMap tw;
     if (make_map_2d(&tw, w2, 64, 576, 576, 64) != 0) return -1;
     StemParams p;
-    p.img = image; p.B = B; p.C = C; p.H = H; p.W = W;
+    p.img = image; p.u8 = u8; p.B = B; p.C = C; p.H = H; p.W = W;
     p.w1 = w1;
     memcpy(p.par, host_params, sizeof(p.par));
     p.pool = pool;
     p.out = reinterpret_cast<__nv_bfloat16*>(out_nhwc);
     p.tiles_x = (W + 7) / 8; p.tiles_y = (H + 15) / 16;
     return launch_conv_stem(tw, p, num_sms, static_cast<cudaStream_t>(stream));
+}
+int b200_sp_conv_stem(const float* image, int B, int C, int H, int W, const float* w1, const float* host_params,
+                      const void* w2, int pool, void* out_nhwc, b200_stream_t stream) {
+    return conv_stem_any(image, 0, B, C, H, W, w1, host_params, w2, pool, out_nhwc, stream);
+}
+int b200_sp_conv_stem_u8(const unsigned char* image, int B, int C, int H, int W, const float* w1,
+                         const float* host_params, const void* w2, int pool, void* out_nhwc, b200_stream_t stream) {
+    return conv_stem_any(image, 1, B, C, H, W, w1, host_params, w2, pool, out_nhwc, stream);
 }
 int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders, float* out,
                        b200_stream_t stream) {

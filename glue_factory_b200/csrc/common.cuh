@@ -85,6 +85,15 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// uint8 pixel -> float32(value / 255.0), the reference's host conversion (utils/image.py:121), without a division:
+// product with the rounded reciprocal plus one fused residual correction; equal to the correctly rounded quotient for
+// all 256 values (checked exhaustively on the host and by tests/test_gpu_dense.py)
+__device__ __forceinline__ float u8_unit(unsigned char v) {
+    const float f = (float)v, r = 0.003921568859368563f;
+    const float q = f * r;
+    return fmaf(fmaf(-255.0f, q, f), r, q);
+}
+
 // 1024-byte alignment of the dynamic shared-memory base by pointer arithmetic on the __shared__ array: a round
 // trip through uintptr_t hides the address space from the compiler, which then emits generic LD / ST (long
 // scoreboard) for every shared-memory access derived from the pointer.

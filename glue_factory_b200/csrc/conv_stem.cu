@@ -62,6 +62,7 @@ __device__ __forceinline__ void st_split(float v, float& hi, float& lo) {
     lo = v - hi;
 }
 
+template <bool U8>
 __global__ void __launch_bounds__(kStThreads, 1)
 conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -319,25 +320,38 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         const bool builder = quarter >= 2;
         const int bt = (((warp - 6) >> 2) * 2 + (quarter - 2)) * 32 + lane;
         // gray pixel e (of 20 x 12) under the patch of tile t, zero outside the image
-        auto load_img = [&](const StTile& c, int e) {
+        // gray pixel e (of 20 x 12) under the patch of tile t, zero outside the image.  Returned RAW (float bits, or
+        // the byte of a single-channel uint8 image) and converted by cook() where it is consumed: the request for the
+        // tile after next stays in flight for a whole tile, a conversion at the load would wait for it on the spot.
+        auto px = [&](long long at) {
+            return U8 ? u8_unit(__ldg(static_cast<const unsigned char*>(p.img) + at))
+                      : __ldg(static_cast<const float*>(p.img) + at);
+        };
+        auto load_img = [&](const StTile& c, int e) -> uint32_t {
             const int b = c.b, ty = c.ty, tx = c.tx;
-            const float* base = p.img + (long long)b * p.C * plane;
+            const long long img0 = (long long)b * p.C * plane;
             const int iy = e / kStImgW, ix = e - iy * kStImgW;
             const int yy = ty * kStTileH - 2 + iy, xx = tx * kStTileW - 2 + ix;
-            float v = 0.f;
+            uint32_t raw = 0u;  // 0.0f and byte 0 alike
             if (e < kStImgH * kStImgW && yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
-                const long long o = (long long)yy * p.W + xx;
+                const long long o = img0 + (long long)yy * p.W + xx;
                 if (p.C == 3) {
                     // same association order as (image * [0.299, 0.587, 0.114]).sum(1)
-                    v = __ldg(base + o) * 0.299f;
-                    v += __ldg(base + o + plane) * 0.587f;
-                    v += __ldg(base + o + 2 * plane) * 0.114f;
+                    float v = px(o) * 0.299f;
+                    v += px(o + plane) * 0.587f;
+                    v += px(o + 2 * plane) * 0.114f;
+                    raw = __float_as_uint(v);
+                } else if (U8) {
+                    raw = __ldg(static_cast<const unsigned char*>(p.img) + o);
                 } else {
-                    v = __ldg(base + o);
+                    raw = __float_as_uint(__ldg(static_cast<const float*>(p.img) + o));
                 }
             }
-            return v;
+            return raw;
         };
+        // uint8 pixels: u8_unit(value) == float32(value / 255.0) of the host conversion (numpy_image_to_torch,
+        // utils/image.py:121) for all 256 values
+        auto cook = [&](uint32_t raw) { return (U8 && p.C == 1) ? u8_unit((unsigned char)raw) : __uint_as_float(raw); };
         // im2col rows of patch pixels bt, bt + 128 for the tile whose pixels are staged in img_s:
         // [hi(9) | lo(9) | hi(9) | 0], written to K columns [32 par, 32 par + 32) of the pixel's row
         // (chunks 4 par .. 4 par + 3 under the 128-byte swizzle)
@@ -369,12 +383,12 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             __syncwarp();
             if (lane == 0) mbar_arrive(a_full + par);
         };
-        float nxt0 = 0.f, nxt1 = 0.f;
+        uint32_t nxt0 = 0u, nxt1 = 0u;
         StTile cur = decomp((int)blockIdx.x);  // tile t of the loop below
         StTile pf = cur;                       // tile whose image pixels are requested next
         if (builder && blockIdx.x < total_tiles) {
-            sImg[bt] = load_img(pf, bt);
-            sImg[bt + 128] = load_img(pf, bt + 128);
+            sImg[bt] = cook(load_img(pf, bt));
+            sImg[bt + 128] = cook(load_img(pf, bt + 128));
             st_build_bar();
             im2col(sImg, 0);
             advance(pf);
@@ -391,8 +405,8 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             const int y0 = ty * kStTileH - 1, x0 = tx * kStTileW - 1;  // image position of patch pixel (0, 0)
             // ---- next tile first: its stem GEMM then runs while this tile's patch is written ----
             if (builder && t + gridDim.x < total_tiles) {
-                sImg[(st ^ 1) * 256 + bt] = nxt0;
-                sImg[(st ^ 1) * 256 + bt + 128] = nxt1;
+                sImg[(st ^ 1) * 256 + bt] = cook(nxt0);
+                sImg[(st ^ 1) * 256 + bt + 128] = cook(nxt1);
                 st_build_bar();  // the next tile's image pixels are staged
                 im2col(sImg + (st ^ 1) * 256, st ^ 1);
                 advance(pf);  // tile t + 2 grid strides
@@ -441,14 +455,16 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
 int launch_conv_stem(const CUtensorMap& tw, const StemParams& p, int num_sms, cudaStream_t stream) {
     static PerDeviceSize configured;
     if (!configured.cur()) {
-        B200_CHECK_CUDA(cudaFuncSetAttribute(conv_stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStSmemBytes));
+        B200_CHECK_CUDA(cudaFuncSetAttribute(conv_stem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStSmemBytes));
+        B200_CHECK_CUDA(cudaFuncSetAttribute(conv_stem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStSmemBytes));
         configured.cur() = 1;
     }
     const long long total = (long long)p.B * p.tiles_x * p.tiles_y;
     if (total == 0) return 0;
     B200_REQUIRE(total < (1ll << 31), "conv_stem: too many tiles");
     const int grid = (int)(total < num_sms ? total : num_sms);
-    B200_CHECK_CUDA(launch_pdl(conv_stem_kernel, dim3(grid), dim3(kStThreads), kStSmemBytes, stream, tw, p));
+    if (p.u8) B200_CHECK_CUDA(launch_pdl(conv_stem_kernel<true>, dim3(grid), dim3(kStThreads), kStSmemBytes, stream, tw, p));
+    else B200_CHECK_CUDA(launch_pdl(conv_stem_kernel<false>, dim3(grid), dim3(kStThreads), kStSmemBytes, stream, tw, p));
     return 0;
 }
 

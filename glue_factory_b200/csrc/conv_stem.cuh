@@ -5,7 +5,8 @@
 namespace b200 {
 
 struct StemParams {
-    const float* img;  // [B, C, H, W] fp32, C = 1 or 3
+    const void* img;   // [B, C, H, W], C = 1 or 3: fp32 in [0, 1], or uint8 (u8 != 0) converted as value / 255
+    int u8;
     int B, C, H, W;
     const float* w1;   // first convolution [64, 9] fp32 (device)
     // per-channel epilogue operands, carried in the kernel parameters (constant bank, no loads in the epilogues):

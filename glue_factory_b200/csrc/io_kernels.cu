@@ -31,8 +31,9 @@ __device__ __forceinline__ int reflect_index(int i, int n) {  // F.pad(mode="ref
     return i;
 }
 
-// u8 -> float exactly as numpy_image_to_torch does it (image.py:121: image / 255.0 in float64, then float32)
-__device__ __forceinline__ float u8_to_unit(unsigned char v) { return static_cast<float>(static_cast<double>(v) / 255.0); }
+// u8 -> float exactly as numpy_image_to_torch does it (image.py:121: image / 255.0 in float64, then float32):
+// u8_unit (common.cuh) reproduces that value for all 256 inputs without a division
+__device__ __forceinline__ float u8_to_unit(unsigned char v) { return u8_unit(v); }
 
 template <bool U8>
 __device__ __forceinline__ float load_src(const PrepParams& p, int b, int c, int y, int x) {

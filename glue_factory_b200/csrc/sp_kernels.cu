@@ -14,27 +14,32 @@ namespace b200 {
 // =============================================================================================
 constexpr int kC1TileW = 32, kC1TileH = 32;
 
-__global__ void __launch_bounds__(256, 2) conv1a_kernel(const float* __restrict__ img, int C, int H, int W,
+__global__ void __launch_bounds__(256, 2) conv1a_kernel(const void* __restrict__ img, int u8, int C, int H, int W,
                                                         const float* __restrict__ w, const float* __restrict__ bias,
                                                         const float* __restrict__ scale, const float* __restrict__ shift,
                                                         __nv_bfloat16* __restrict__ out) {
     __shared__ float tile[kC1TileH + 2][kC1TileW + 2];
     const int tid = threadIdx.x;
     const int b = blockIdx.z, x0 = blockIdx.x * kC1TileW, y0 = blockIdx.y * kC1TileH;
-    const float* base = img + (long long)b * C * H * W;
+    const long long img0 = (long long)b * C * H * W;
+    // uint8 pixels: value / 255 correctly rounded == float32(value / 255.0) of the host conversion (image.py:121)
+    auto pix = [&](long long at) {
+        return u8 ? u8_unit(__ldg(static_cast<const unsigned char*>(img) + at))
+                  : __ldg(static_cast<const float*>(img) + at);
+    };
     for (int i = tid; i < (kC1TileH + 2) * (kC1TileW + 2); i += 256) {
         const int ty = i / (kC1TileW + 2), tx = i - ty * (kC1TileW + 2);
         const int y = y0 + ty - 1, x = x0 + tx - 1;
         float v = 0.f;
         if (y >= 0 && y < H && x >= 0 && x < W) {
-            const long long o = (long long)y * W + x;
+            const long long o = img0 + (long long)y * W + x;
             if (C == 3) {
                 // same association order as (image * [0.299, 0.587, 0.114]).sum(1)
-                v = __ldg(base + o) * 0.299f;
-                v += __ldg(base + o + (long long)H * W) * 0.587f;
-                v += __ldg(base + o + 2ll * H * W) * 0.114f;
+                v = pix(o) * 0.299f;
+                v += pix(o + (long long)H * W) * 0.587f;
+                v += pix(o + 2ll * H * W) * 0.114f;
             } else {
-                v = __ldg(base + o);
+                v = pix(o);
             }
         }
         tile[ty][tx] = v;
@@ -84,12 +89,12 @@ __global__ void __launch_bounds__(256, 2) conv1a_kernel(const float* __restrict_
     }
 }
 
-int launch_conv1a(const float* img, int B, int C, int H, int W, const float* w, const float* bias,
+int launch_conv1a(const void* img, int u8, int B, int C, int H, int W, const float* w, const float* bias,
                   const float* scale, const float* shift, void* out, cudaStream_t stream) {
     B200_REQUIRE(C == 1 || C == 3, "conv1a: image must have 1 or 3 channels, got %d", C);
     if (B == 0) return 0;
     dim3 grid((W + kC1TileW - 1) / kC1TileW, (H + kC1TileH - 1) / kC1TileH, B);
-    conv1a_kernel<<<grid, 256, 0, stream>>>(img, C, H, W, w, bias, scale, shift,
+    conv1a_kernel<<<grid, 256, 0, stream>>>(img, u8, C, H, W, w, bias, scale, shift,
                                             reinterpret_cast<__nv_bfloat16*>(out));
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

@@ -3,7 +3,7 @@
 #include <stdint.h>
 
 namespace b200 {
-int launch_conv1a(const float* img, int B, int C, int H, int W, const float* w, const float* bias,
+int launch_conv1a(const void* img, int u8, int B, int C, int H, int W, const float* w, const float* bias,
                   const float* scale, const float* shift, void* out, cudaStream_t stream);
 int launch_nms_border(const float* scores, int B, int H, int W, int radius, int pad, float* out,
                       cudaStream_t stream);

@@ -58,7 +58,9 @@ def sp_dense_forward(P, image):
     image (B,1|3,H,W) fp32 -> heat map (B,8h,8w) fp32, dense descriptors NHWC (B,h,w,256) fp32."""
     if not image.is_cuda:
         raise RuntimeError("glue_factory_b200 SuperPoint runs on CUDA only (no CPU fallback)")
-    image = image.float().contiguous()
+    # uint8 pixels (as read from disk) are converted in the first kernel's load: value / 255, bit-identical to the
+    # reference's host conversion (utils/image.py:112-121); anything else follows the float [0, 1] contract
+    image = image.contiguous() if image.dtype == torch.uint8 else image.float().contiguous()
     B, _, H, W = image.shape
     dev = image.device
     L0 = P["convs"][0]

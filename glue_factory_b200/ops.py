@@ -165,8 +165,9 @@ def attention(q, k, v, seqs, *, num_seqs, max_q_len, heads, ldq, ldk, ldv, q_col
 def sp_conv1a(image, w, bias, scale, shift, out):
     _require_cuda(image, out)
     b, c, h, wd = image.shape
+    fn = _lib.lib().b200_sp_conv1a_u8 if image.dtype == torch.uint8 else _lib.lib().b200_sp_conv1a
     with _timed("sp_conv1a", 1, 2.0 * b * h * wd * 64 * 9):
-        _lib.check(_lib.lib().b200_sp_conv1a(_ptr(image), b, c, h, wd, _ptr(w), _ptr(bias), _ptr(scale), _ptr(shift),
+        _lib.check(fn(_ptr(image), b, c, h, wd, _ptr(w), _ptr(bias), _ptr(scale), _ptr(shift),
                                              _ptr(out), _stream()))
 
 
@@ -178,8 +179,9 @@ def sp_conv_stem(image, w1, host_params, w2, pool, out):
         raise ValueError("sp_conv_stem: host_params must be a CPU float32 tensor of shape (6, 64)")
     host_params = host_params.contiguous()
     b, c, h, wd = image.shape
+    fn = _lib.lib().b200_sp_conv_stem_u8 if image.dtype == torch.uint8 else _lib.lib().b200_sp_conv_stem
     with _timed("sp_conv_stem", 1, 2.0 * b * h * wd * 64 * (9 + 576)):
-        _lib.check(_lib.lib().b200_sp_conv_stem(_ptr(image), b, c, h, wd, _ptr(w1), host_params.data_ptr(), _ptr(w2),
+        _lib.check(fn(_ptr(image), b, c, h, wd, _ptr(w1), host_params.data_ptr(), _ptr(w2),
                                                 int(pool), _ptr(out), _stream()))
 
 

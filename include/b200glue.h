@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 8
+#define B200_ABI_VERSION 9
 
 typedef void* b200_stream_t; /* cudaStream_t */
 
@@ -115,6 +115,13 @@ int b200_sp_conv1a(const float* image, int B, int C, int H, int W, const float* 
 int b200_sp_conv_stem(const float* image, int B, int C, int H, int W, const float* w1 /*[64,9] device*/,
                       const float* host_params /*[6][64] host*/, const void* w2, int pool, void* out_nhwc,
                       b200_stream_t stream);
+/* the two entries above on uint8 images [B,C,H,W] (pixels as read from disk): the conversion value / 255 of
+ * numpy_image_to_torch (gluefactory/utils/image.py:112-121) is done in the load, bit-identical to the host conversion,
+ * so a loader ships a quarter of the bytes */
+int b200_sp_conv1a_u8(const unsigned char* image, int B, int C, int H, int W, const float* w, const float* bias,
+                      const float* scale, const float* shift, void* out_nhwc, b200_stream_t stream);
+int b200_sp_conv_stem_u8(const unsigned char* image, int B, int C, int H, int W, const float* w1,
+                         const float* host_params, const void* w2, int pool, void* out_nhwc, b200_stream_t stream);
 /* batched_nms (:34-49) + border removal (:147-152); out has the shape of scores */
 int b200_sp_nms_border(const float* scores, int B, int H, int W, int nms_radius, int remove_borders,
                        float* out, b200_stream_t stream);

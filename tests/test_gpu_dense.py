@@ -237,3 +237,31 @@ def test_attention(dev, lens):
             ref = _attn_ref(qb[q0:q0 + ql, hd * 64:(hd + 1) * 64], kvb[k0:k0 + kl, 256 + hd * 64:256 + (hd + 1) * 64],
                             kvb[k0:k0 + kl, 512 + hd * 64:512 + (hd + 1) * 64], 0.125)
             _close(out[q0:q0 + ql, hd * 64:(hd + 1) * 64], ref, 2e-2, 2e-2, f"attention head {hd}")
+
+
+def test_uint8_images_equal_the_float_contract(dev, sp_weights, tmp_path):
+    """uint8 pixels converted in the first kernel's load (value / 255) give bit-identical results to the float32
+    images the reference's loader produces (utils/image.py:112-121), gray and RGB, fused stem and stand-alone conv1a."""
+    from glue_factory_b200 import ops
+    from gluefactory.models import get_model
+
+    torch.save(sp_weights, tmp_path / "sp.pth")
+    model = get_model("extractors.superpoint_open")({"weights": str(tmp_path / "sp.pth"), "max_num_keypoints": 128,
+                                                      "detection_threshold": -1, "nms_radius": 3}).to(dev).eval()
+    g = torch.Generator().manual_seed(1)
+    for c in (1, 3):
+        u8 = torch.randint(0, 256, (2, c, 96, 160), generator=g, dtype=torch.uint8)
+        u8[0, 0, 40, :] = torch.arange(160, dtype=torch.uint8)          # every value 0..255 occurs
+        u8[0, 0, 41, :96] = torch.arange(160, 256, dtype=torch.uint8)
+        f32 = torch.from_numpy((u8.numpy() / 255.0).astype("float32"))
+        with torch.no_grad():
+            a = model({"image": u8.to(dev)})
+            b = model({"image": f32.to(dev)})
+        for k in ("heatmap", "keypoints", "keypoint_scores", "descriptors"):
+            assert torch.equal(a[k], b[k]), (c, k)
+        P = model._pack()
+        o1 = torch.empty(2, 96, 160, 64, dtype=torch.bfloat16, device=dev)
+        o2 = torch.empty_like(o1)
+        ops.sp_conv1a(u8.to(dev), P["c1a_w"], P["c1a_b"], P["c1a_s"], P["c1a_t"], o1)
+        ops.sp_conv1a(f32.to(dev), P["c1a_w"], P["c1a_b"], P["c1a_s"], P["c1a_t"], o2)
+        assert torch.equal(o1, o2)

@@ -76,6 +76,16 @@ def test_preprocessor_full_size_vs_oracle(dev, hw, conf):
     assert np.array_equal(out["image_size"], ref["image_size"])
 
 
+def test_uint8_conversion_is_exact_for_all_values(dev):
+    """value / 255 of every uint8 value equals numpy_image_to_torch's float32(value / 255.0) bit for bit (the same
+    device function converts the pixels in the SuperPoint stem kernels)."""
+    from gluefactory.utils.image import ImagePreprocessor
+
+    u8 = torch.arange(256, dtype=torch.uint8).view(16, 16)
+    out = ImagePreprocessor(dict(resize=None))(u8.to(dev))["image"].cpu()
+    assert torch.equal(out, opre.numpy_image_to_torch(u8.numpy()))
+
+
 def test_preprocessor_rejects_unsupported(dev):
     from gluefactory.utils.image import ImagePreprocessor
 
