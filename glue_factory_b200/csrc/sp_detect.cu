@@ -30,7 +30,6 @@ constexpr int kEW = 128, kEH = NMS_EH, kSeg = 16;
 #define NMS_THREADS 768
 #endif
 constexpr int kNmsFastThreads = NMS_THREADS;
-constexpr int kMaskWords = 6;  // [guard | 4 words = 128 columns | guard]
 
 __device__ __forceinline__ uint32_t order_key32(float v) {
     const uint32_t u = __float_as_uint(v);
@@ -72,15 +71,15 @@ struct NmsGeom {
     static constexpr int kTileW = kEW - 10 * R, kTileH = kEH - 10 * R;
     static constexpr int kSFloats = kEH * kPitchS;
     static constexpr int kTFloats = (kEH + 2 * R) * kPitchT;
-    static constexpr int kMaskRows = kEH + 2 * R;
-    static constexpr size_t kSmemBytes =
-        (size_t)(kSFloats + kTFloats) * 4 + (size_t)(kMaskRows + kEH) * kMaskWords * 4;
+    static constexpr int kPitchM = kEW + 2 * R;                 // halfword masks: R zero guard columns each side
+    static constexpr int kMaskHalfs = (kEH / kSeg) * kPitchM;   // per mask array (even: cleared as 32-bit words)
+    static constexpr size_t kSmemBytes = (size_t)(kSFloats + kTFloats) * 4 + (size_t)2 * kMaskHalfs * 2;
 };
 
-// row pass: tmp[y][x] = max_{|dx|<=R} src(y, x+dx), src = s or (supp ? 0 : s)
-template <int R, bool MASKED>
-__device__ __forceinline__ void row_pass(const float* __restrict__ s, float* __restrict__ tmp,
-                                         const uint32_t* __restrict__ supp) {
+// row pass: tmp[y][x] = max_{|dx|<=R} s(y, x+dx).  In the refinement rounds `s` already holds the suppressed scores
+// (apply_supp), so the pass is the same in every round.
+template <int R>
+__device__ __forceinline__ void row_pass(const float* __restrict__ s, float* __restrict__ tmp) {
     using G = NmsGeom<R>;
     for (int item = threadIdx.x; item < kEH * (kEW / kSeg); item += kNmsFastThreads) {
         const int y = item % kEH, x0 = (item / kEH) * kSeg;
@@ -88,15 +87,6 @@ __device__ __forceinline__ void row_pass(const float* __restrict__ s, float* __r
         const float* row = s + y * G::kPitchS + x0;  // column x0-R of the image window (array is shifted by R)
 #pragma unroll
         for (int j = 0; j < kSeg + 2 * R; ++j) v[j] = row[j];
-        if constexpr (MASKED) {
-            // 32 suppression bits starting at column x0-R (guard words are zero)
-            const int p = x0 - R + 32;
-            const uint32_t* w = supp + y * kMaskWords + (p >> 5);
-            const uint32_t bits = __funnelshift_r(w[0], w[1], p & 31);
-#pragma unroll
-            for (int j = 0; j < kSeg + 2 * R; ++j)
-                if (((bits >> j) & 1u) && v[j] != -INFINITY) v[j] = 0.f;  // padding stays -inf
-        }
         window_max<R>(v, o);
         float* dst = tmp + (y + R) * G::kPitchT + x0;
 #pragma unroll
@@ -104,50 +94,65 @@ __device__ __forceinline__ void row_pass(const float* __restrict__ s, float* __r
     }
 }
 
+// The max / suppression masks are kept as 16-bit words ALONG y: halfword (h, x) holds rows 16 h .. 16 h + 15 of column
+// x, stored [h][R guard | kEW columns | R guard].  A thread of the column pass owns exactly one halfword (no ballots,
+// no shared read-modify-write between lanes), the dilation works on whole halfwords, and the suppression is applied
+// by the thread that computed it.
+
 // column pass + comparison: bit(y, x) = s == max_{|dy|<=R} tmp(y+dy, x) [and not suppressed]
 template <int R, bool ROUND>
 __device__ __forceinline__ void col_pass(const float* __restrict__ s, const float* __restrict__ tmp,
-                                         uint32_t* __restrict__ mask, const uint32_t* __restrict__ supp) {
+                                         uint16_t* __restrict__ maskh, const uint16_t* __restrict__ supph) {
     using G = NmsGeom<R>;
-    const int lane = threadIdx.x & 31;
     for (int item = threadIdx.x; item < kEW * (kEH / kSeg); item += kNmsFastThreads) {
-        const int x = item & (kEW - 1), y0 = (item / kEW) * kSeg;
+        const int x = item & (kEW - 1), h = item / kEW, y0 = h * kSeg;
         float v[kSeg + 2 * R], o[kSeg];
 #pragma unroll
         for (int j = 0; j < kSeg + 2 * R; ++j) v[j] = tmp[(y0 + j) * G::kPitchT + x];
         window_max<R>(v, o);
-        const int word = 1 + (x >> 5);  // warp-uniform
+        uint32_t bits = 0u;
 #pragma unroll
         for (int i = 0; i < kSeg; ++i) {
             const float sv = s[(y0 + i) * G::kPitchS + R + x];
-            bool c = sv != -INFINITY && sv == o[i];  // out-of-image pixels never become maxima
-            if constexpr (ROUND) c = c && !((supp[(y0 + i) * kMaskWords + word] >> lane) & 1u);
-            const uint32_t b = __ballot_sync(0xffffffffu, c);
-            if (lane == 0) {
-                uint32_t* m = mask + (y0 + i + R) * kMaskWords + word;
-                *m = ROUND ? (*m | b) : b;
-            }
+            bits |= (sv != -INFINITY && sv == o[i]) ? (1u << i) : 0u;  // out-of-image pixels never become maxima
         }
+        uint16_t* m = maskh + h * G::kPitchM + R + x;
+        if constexpr (ROUND) *m = (uint16_t)(*m | (bits & ~(uint32_t)supph[h * G::kPitchM + R + x]));
+        else *m = (uint16_t)bits;
     }
 }
 
-// supp = dilate(mask, R) (max_pool of the 0/1 mask > 0)
+// supp = dilate(mask, R) (max_pool of the 0/1 mask > 0), then s <- where(supp, 0, s) in place (padding stays -inf).
+// The suppression mask only grows from round to round, so the second round's where(supp2, 0, s) equals
+// where(supp2, 0, where(supp1, 0, s)): one float buffer serves all rounds; the original scores of the final maxima are
+// re-read from global memory by the output pass.
 template <int R>
-__device__ __forceinline__ void dilate(const uint32_t* __restrict__ mask, uint32_t* __restrict__ supp) {
-    for (int item = threadIdx.x; item < kEH * 4; item += kNmsFastThreads) {
-        const int y = item >> 2, w = 1 + (item & 3);
-        uint32_t l = 0, m = 0, r = 0;
+__device__ __forceinline__ void dilate_apply(const uint16_t* __restrict__ maskh, uint16_t* __restrict__ supph,
+                                             float* __restrict__ s) {
+    using G = NmsGeom<R>;
+    constexpr int kH = kEH / kSeg;
+    for (int item = threadIdx.x; item < kEW * kH; item += kNmsFastThreads) {
+        const int x = item & (kEW - 1), h = item / kEW;
+        uint32_t up = 0u, mid = 0u, dn = 0u;  // rows above / of / below this halfword, OR over the 2R+1 columns
+        const uint16_t* row = maskh + h * G::kPitchM + x;  // column x - R (guard columns are zero)
 #pragma unroll
-        for (int dy = 0; dy <= 2 * R; ++dy) {
-            const uint32_t* row = mask + (y + dy) * kMaskWords + w;  // mask rows are shifted by R
-            l |= row[-1];
-            m |= row[0];
-            r |= row[1];
+        for (int dx = 0; dx <= 2 * R; ++dx) {
+            mid |= row[dx];
+            if (h > 0) up |= row[dx - G::kPitchM];
+            if (h < kH - 1) dn |= row[dx + G::kPitchM];
         }
-        uint32_t d = m;
+        const unsigned long long c = (unsigned long long)up | ((unsigned long long)mid << 16) | ((unsigned long long)dn << 32);
+        unsigned long long d = c;
 #pragma unroll
-        for (int k = 1; k <= R; ++k) d |= (m << k) | (l >> (32 - k)) | (m >> k) | (r << (32 - k));
-        supp[y * kMaskWords + w] = d;
+        for (int k = 1; k <= R; ++k) d |= (c << k) | (c >> k);
+        const uint32_t sp = (uint32_t)(d >> 16) & 0xffffu;
+        supph[h * G::kPitchM + R + x] = (uint16_t)sp;
+        if (sp != 0u) {
+            float* px = s + (h * kSeg) * G::kPitchS + R + x;
+#pragma unroll
+            for (int i = 0; i < kSeg; ++i)
+                if (((sp >> i) & 1u) && px[i * G::kPitchS] != -INFINITY) px[i * G::kPitchS] = 0.f;
+        }
     }
 }
 
@@ -157,50 +162,68 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const i
                 float* __restrict__ out, unsigned long long* __restrict__ cand, int* __restrict__ cand_count, int cap) {
     using G = NmsGeom<R>;
     extern __shared__ uint8_t nms_fast_smem[];
+    __shared__ int s_count, s_base;
     float* s = reinterpret_cast<float*>(nms_fast_smem);
     float* tmp = s + G::kSFloats;
-    uint32_t* mask = reinterpret_cast<uint32_t*>(tmp + G::kTFloats);  // [kMaskRows][6], rows shifted by R
-    uint32_t* supp = mask + G::kMaskRows * kMaskWords;                // [kEH][6]
+    uint16_t* maskh = reinterpret_cast<uint16_t*>(tmp + G::kTFloats);  // [kEH / 16][kPitchM]
+    uint16_t* supph = maskh + G::kMaskHalfs;
     const int b = blockIdx.z, tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
     const int ox = blockIdx.x * G::kTileW, oy = blockIdx.y * G::kTileH;  // output tile origin
     const int x0 = ox - 5 * R, y0 = oy - 5 * R;                          // staged window origin
     const float* src = scores + (long long)b * H * W;
 
-    for (int i = tid; i < kEH * G::kPitchS; i += kNmsFastThreads) {
-        const int yy = i / G::kPitchS, c = i - yy * G::kPitchS;
-        const int y = y0 + yy, x = x0 + c - R;
-        const bool in = c >= R && c < R + kEW && y >= 0 && y < H && x >= 0 && x < W;
-        s[i] = in ? __ldg(src + (long long)y * W + x) : -INFINITY;
+    // stage the window: one warp per row, lanes along x (coalesced), -inf outside the image and in the R pad columns
+    static_assert(kEH % (kNmsFastThreads / 32) == 0, "whole rows per warp");
+#pragma unroll
+    for (int it = 0; it < kEH / (kNmsFastThreads / 32); ++it) {  // unrolled: all of a warp's row requests in flight
+        const int yy = warp + it * (kNmsFastThreads / 32);
+        const int y = y0 + yy;
+        const bool row_ok = y >= 0 && y < H;
+        const float* grow = src + (long long)y * W;
+        float* srow = s + yy * G::kPitchS;
+#pragma unroll
+        for (int c = lane; c < G::kPitchS; c += 32) {
+            const int x = x0 + c - R;
+            const bool in = row_ok && c >= R && c < R + kEW && x >= 0 && x < W;
+            srow[c] = in ? __ldg(grow + x) : -INFINITY;
+        }
     }
     for (int i = tid; i < R * G::kPitchT; i += kNmsFastThreads) {
         tmp[i] = -INFINITY;
         tmp[(kEH + R) * G::kPitchT + i] = -INFINITY;
     }
-    for (int i = tid; i < (G::kMaskRows + kEH) * kMaskWords; i += kNmsFastThreads) mask[i] = 0u;
+    for (int i = tid; i < 2 * G::kMaskHalfs / 2; i += kNmsFastThreads) reinterpret_cast<uint32_t*>(maskh)[i] = 0u;
+    if (tid == 0) s_count = 0;
     __syncthreads();
 
-    row_pass<R, false>(s, tmp, nullptr);
+    row_pass<R>(s, tmp);
     __syncthreads();
-    col_pass<R, false>(s, tmp, mask, nullptr);
+    col_pass<R, false>(s, tmp, maskh, nullptr);
     __syncthreads();
 #pragma unroll 1
     for (int round = 0; round < 2; ++round) {
-        dilate<R>(mask, supp);
+        dilate_apply<R>(maskh, supph, s);
         __syncthreads();
-        row_pass<R, true>(s, tmp, supp);
+        row_pass<R>(s, tmp);
         __syncthreads();
-        col_pass<R, true>(s, tmp, mask, supp);
+        col_pass<R, true>(s, tmp, maskh, supph);
         __syncthreads();
     }
 
-    const int lane = tid & 31;
     // bottom / right border from the per-image valid size when given (gluefactory_nonfree/superpoint.py:244-254)
     const int bh = image_hw ? image_hw[2 * b] : H, bw = image_hw ? image_hw[2 * b + 1] : W;
     float* dst = out + (long long)b * H * W;
     unsigned long long* list = cand ? cand + (long long)b * cap : nullptr;
-    // one warp per output row segment of 32 columns
+    // candidate records of this tile are collected in shared memory (the score window and the pooling scratch are
+    // free now and hold kTileW * kTileH records) and appended to the image's list with ONE global atomic per CTA
+    unsigned long long* rec = reinterpret_cast<unsigned long long*>(s);
+    static_assert((size_t)G::kTileW * G::kTileH * 8 <= (size_t)(G::kSFloats + G::kTFloats) * 4,
+                  "candidate records must fit the window + scratch");
+    // one warp per output row segment of 32 columns; the maxima's scores come from global memory (the staged copy
+    // was overwritten by the suppression): a few percent of the pixels, L2 hits
     constexpr int kSegs = (G::kTileW + 31) / 32;
-    for (int item = tid >> 5; item < G::kTileH * kSegs; item += kNmsFastThreads / 32) {
+    for (int item = warp; item < G::kTileH * kSegs; item += kNmsFastThreads / 32) {
         const int ty = item / kSegs, tx = (item - ty * kSegs) * 32 + lane;
         const int y = oy + ty, x = ox + tx;
         const bool valid = tx < G::kTileW && y < H && x < W;
@@ -208,9 +231,8 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const i
         float v = 0.f;
         bool keep = false;
         if (valid) {
-            const bool mx = (mask[(ey + R) * kMaskWords + 1 + (ex >> 5)] >> (ex & 31)) & 1u;
-            const float sv = s[ey * G::kPitchS + R + ex];
-            v = mx ? sv : 0.f;
+            const bool mx = (maskh[(ey >> 4) * G::kPitchM + R + ex] >> (ey & 15)) & 1u;
+            if (mx) v = __ldg(src + (long long)y * W + x);
             const bool border = pad > 0 && (y < pad || x < pad || y >= bh - pad || x >= bw - pad);
             if (border) v = -1.f;
             dst[(long long)y * W + x] = v;
@@ -220,13 +242,23 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const i
             const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
             if (ballot != 0u) {
                 int base = 0;
-                if (lane == 0) base = atomicAdd(cand_count + b, __popc(ballot));
+                if (lane == 0) base = atomicAdd(&s_count, __popc(ballot));
                 base = __shfl_sync(0xffffffffu, base, 0);
-                const int slot = base + __popc(ballot & ((1u << lane) - 1u));
-                if (keep && slot < cap)
-                    list[slot] = (static_cast<unsigned long long>(order_key32(v)) << 32) |
-                                 ~static_cast<uint32_t>(y * W + x);
+                if (keep)
+                    rec[base + __popc(ballot & ((1u << lane) - 1u))] =
+                        (static_cast<unsigned long long>(order_key32(v)) << 32) | ~static_cast<uint32_t>(y * W + x);
             }
+        }
+    }
+    if (list != nullptr) {
+        __syncthreads();
+        const int n = s_count;
+        if (n > 0) {
+            if (tid == 0) s_base = atomicAdd(cand_count + b, n);  // the count keeps growing past `cap`: overflow flag
+            __syncthreads();
+            const int base = s_base;
+            for (int i = tid; i < n; i += kNmsFastThreads)
+                if (base + i < cap) list[base + i] = rec[i];
         }
     }
 }
