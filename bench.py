@@ -116,6 +116,13 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def quiet_nccl():
+    """NCCL writes its version banner to STDOUT at NCCL_DEBUG=VERSION and above (WARN included); stdout must carry
+    the one JSON line only.  Unset means silent; an explicit VERSION / WARN request is downgraded."""
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "WARN"):
+        os.environ["NCCL_DEBUG"] = "NONE"
+
+
 def dist_env():
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     return rank, world, int(os.environ.get("LOCAL_RANK", 0))
@@ -399,9 +406,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # NCCL prints its version banner on stdout at the VERSION level: keep stdout to the one JSON line
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        quiet_nccl()
         dist.init_process_group("nccl", device_id=dev)
     steps, warmup = args.steps, max(3, args.warmup)
     sp_path, lg_path = weight_files()
@@ -664,8 +669,7 @@ def run_workload(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        quiet_nccl()
         dist.init_process_group("nccl", device_id=dev)
     P, K = wl["pairs"], wl["kpts"]
     steps, warmup = args.steps, max(3, args.warmup)

@@ -158,6 +158,7 @@ class LightGlue(nn.Module):
             self.load_state_dict(state_dict, strict=False)
         self._packed = None
         self._packed_key = None
+        self._seq_cache = {}
         self.layer_tap = None  # set to a list to collect the residual stream after every layer (tests)
 
     def compile(self, mode="reduce-overhead"):
@@ -299,6 +300,21 @@ class LightGlue(nn.Module):
             layer = self.conf.n_layers - 1 if layer is None else layer
             return self._assign(P["assign"][layer], ws, B, M, N, T)[:5]
 
+    def _seqs(self, B, M, N, dev):
+        """Attention problem lists of a (B, M, N) batch: self (each image with itself) and cross (both directions),
+        with len_override slots (b, B + b) for the adaptive mode.  Built once per shape and kept on the device."""
+        key = (B, M, N, str(dev))
+        if key not in self._seq_cache:
+            off1 = B * M
+            if len(self._seq_cache) > 16:
+                self._seq_cache.clear()
+            self._seq_cache[key] = (
+                ops.make_attn_seqs([(b * M, M, b * M, M, b, b) for b in range(B)] +
+                                   [(off1 + b * N, N, off1 + b * N, N, B + b, B + b) for b in range(B)], dev),
+                ops.make_attn_seqs([(b * M, M, off1 + b * N, N, b, B + b) for b in range(B)] +
+                                   [(off1 + b * N, N, b * M, M, B + b, b) for b in range(B)], dev))
+        return self._seq_cache[key]
+
     def _workspace(self, T, dev, zero=False):
         """`zero`: adaptive mode keeps dead rows in the buffers (pruned tokens, skipped tiles); they must hold finite
         values because the attention kernel multiplies masked keys' V rows by exact zeros."""
@@ -350,11 +366,7 @@ class LightGlue(nn.Module):
         ops.lg_ingest(desc1, ws["x32"], ws["xm"], 512, row0=B * M)
         ops.lg_posenc(kpts0.float().contiguous(), _size(size0, dev, B), P["wr"], ws["cs"], row0=0)
         ops.lg_posenc(kpts1.float().contiguous(), _size(size1, dev, B), P["wr"], ws["cs"], row0=B * M)
-        off1 = B * M
-        seqs_self = ops.make_attn_seqs(
-            [(b * M, M, b * M, M) for b in range(B)] + [(off1 + b * N, N, off1 + b * N, N) for b in range(B)], dev)
-        seqs_cross = ops.make_attn_seqs(
-            [(b * M, M, off1 + b * N, N) for b in range(B)] + [(off1 + b * N, N, b * M, M) for b in range(B)], dev)
+        seqs_self, seqs_cross = self._seqs(B, M, N, dev)
         for i in range(self.conf.n_layers):
             # algorithmic FLOPs: self 1024 n^2 per image, cross 1536 M N per pair (sim counted once)
             self._layer(P["layers"][i], ws, T, seqs_self, seqs_cross, 2 * B, max(M, N),
@@ -371,8 +383,8 @@ class LightGlue(nn.Module):
             "ref_descriptors0": x[: B * M].view(B, 1, M, 256),
             "ref_descriptors1": x[B * M:].view(B, 1, N, 256),
             "log_assignment": scores,
-            "prune0": torch.ones_like(ms0) * self.conf.n_layers,
-            "prune1": torch.ones_like(ms1) * self.conf.n_layers,
+            "prune0": torch.full_like(ms0, self.conf.n_layers),
+            "prune1": torch.full_like(ms1, self.conf.n_layers),
         }
 
     def loss(self, pred, data):

@@ -72,10 +72,7 @@ def adaptive_forward(model, data, kpts0, kpts1, desc0, desc1, size0, size1):
     ind_final = torch.zeros(T, **i32)
     final_len = torch.zeros(2 * B, **i32)
 
-    seqs_self = ops.make_attn_seqs([(b * M, M, b * M, M, b, b) for b in range(B)] +
-                                   [(off1 + b * N, N, off1 + b * N, N, B + b, B + b) for b in range(B)], dev)
-    seqs_cross = ops.make_attn_seqs([(b * M, M, off1 + b * N, N, b, B + b) for b in range(B)] +
-                                    [(off1 + b * N, N, b * M, M, B + b, b) for b in range(B)], dev)
+    seqs_self, seqs_cross = model._seqs(B, M, N, dev)
     ops.lg_adaptive_commit(state, None, B, M, N, lens, tile_live, hist[0])
 
     for i in range(L):
@@ -120,8 +117,8 @@ def adaptive_forward(model, data, kpts0, kpts1, desc0, desc1, size0, size1):
         ops.lg_adaptive_scatter(m0, m1, ms0, ms1, ind_final, final_len, B, M, N, out_m0, out_m1, out_ms0, out_ms1)
         m0, m1, ms0, ms1 = out_m0, out_m1, out_ms0, out_ms1
     else:
-        prune0 = torch.ones_like(ms0) * L
-        prune1 = torch.ones_like(ms1) * L
+        prune0 = torch.full_like(ms0, L)
+        prune1 = torch.full_like(ms1, L)
     model.adaptive_stats = {"hist": hist, "state": state, "final_len": final_len, "M": M, "N": N}  # device tensors
 
     # the one read-back of the pass: final live sizes (output shapes of a B = 1 call, fully pruned images)
