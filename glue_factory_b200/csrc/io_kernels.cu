@@ -41,91 +41,73 @@ __device__ __forceinline__ float load_src(const PrepParams& p, int b, int c, int
     return static_cast<const float*>(p.src)[(((long long)b * p.C + c) * p.H + y) * p.W + x];
 }
 
+// The three kernels below use a 3-D grid (x blocks, row, image * channel): no per-element division.
+
 // horizontal Gaussian pass over the source: tmp[b,c,y,x] = sum_k tx[k] * src[b,c,y,reflect(x + k - r)]
 template <bool U8>
 __global__ void __launch_bounds__(256) prep_hblur_kernel(const __grid_constant__ PrepParams p) {
-    const long long total = (long long)p.B * p.C * p.H * p.W;
+    const int x = blockIdx.x * 256 + threadIdx.x, y = blockIdx.y;
+    const int b = blockIdx.z / p.C, c = blockIdx.z - b * p.C;
+    if (x >= p.W) return;
     const int r = p.kx / 2;
-    for (long long t = (long long)blockIdx.x * 256 + threadIdx.x; t < total; t += (long long)gridDim.x * 256) {
-        const int x = (int)(t % p.W);
-        long long q = t / p.W;
-        const int y = (int)(q % p.H);
-        q /= p.H;
-        const int c = (int)(q % p.C), b = (int)(q / p.C);
-        float acc = 0.f;
-        for (int k = 0; k < p.kx; ++k) acc = fmaf(p.tx[k], load_src<U8>(p, b, c, y, reflect_index(x + k - r, p.W)), acc);
-        p.tmp[t] = acc;
-    }
+    float acc = 0.f;
+    for (int k = 0; k < p.kx; ++k) acc = fmaf(p.tx[k], load_src<U8>(p, b, c, y, reflect_index(x + k - r, p.W)), acc);
+    p.tmp[(((long long)b * p.C + c) * p.H + y) * p.W + x] = acc;
 }
 
 // vertical Gaussian pass fused with the bilinear resize and the padding: one thread per output pixel
 template <bool U8, bool BLUR>
 __global__ void __launch_bounds__(256) prep_resize_kernel(const __grid_constant__ PrepParams p) {
-    const long long total = (long long)p.B * p.C * p.pad_h * p.pad_w;
+    const int ox = blockIdx.x * 256 + threadIdx.x, oy = blockIdx.y;
+    const int b = blockIdx.z / p.C, c = blockIdx.z - b * p.C;
+    if (ox >= p.pad_w) return;
     const int r = p.ky / 2;
-    for (long long t = (long long)blockIdx.x * 256 + threadIdx.x; t < total; t += (long long)gridDim.x * 256) {
-        const int ox = (int)(t % p.pad_w);
-        long long q = t / p.pad_w;
-        const int oy = (int)(q % p.pad_h);
-        q /= p.pad_h;
-        const int c = (int)(q % p.C), b = (int)(q / p.C);
-        const bool inside = oy < p.out_h && ox < p.out_w;
-        if (p.mask != nullptr && c == 0) p.mask[((long long)b * p.pad_h + oy) * p.pad_w + ox] = inside ? 1 : 0;
-        float v = 0.f;
-        if (inside) {
-            // area_pixel_compute_source_index, align_corners=False: src = scale * (dst + 0.5) - 0.5, clamped at 0
-            float sy = p.scale_y * (oy + 0.5f) - 0.5f, sx = p.scale_x * (ox + 0.5f) - 0.5f;
-            sy = sy < 0.f ? 0.f : sy;
-            sx = sx < 0.f ? 0.f : sx;
-            const int y0 = (int)sy, x0 = (int)sx;
-            const int y1 = y0 + (y0 < p.H - 1 ? 1 : 0), x1 = x0 + (x0 < p.W - 1 ? 1 : 0);
-            const float ly1 = sy - y0, lx1 = sx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
-            float v00, v01, v10, v11;
-            if (BLUR) {
-                const float* tp = p.tmp + ((long long)b * p.C + c) * p.H * p.W;
-                v00 = v01 = v10 = v11 = 0.f;
-                for (int k = 0; k < p.ky; ++k) {
-                    const long long ra = (long long)reflect_index(y0 + k - r, p.H) * p.W;
-                    const long long rb = (long long)reflect_index(y1 + k - r, p.H) * p.W;
-                    const float w = p.ty[k];
-                    v00 = fmaf(w, tp[ra + x0], v00);
-                    v01 = fmaf(w, tp[ra + x1], v01);
-                    v10 = fmaf(w, tp[rb + x0], v10);
-                    v11 = fmaf(w, tp[rb + x1], v11);
-                }
-            } else {
-                v00 = load_src<U8>(p, b, c, y0, x0);
-                v01 = load_src<U8>(p, b, c, y0, x1);
-                v10 = load_src<U8>(p, b, c, y1, x0);
-                v11 = load_src<U8>(p, b, c, y1, x1);
+    const bool inside = oy < p.out_h && ox < p.out_w;
+    if (p.mask != nullptr && c == 0) p.mask[((long long)b * p.pad_h + oy) * p.pad_w + ox] = inside ? 1 : 0;
+    float v = 0.f;
+    if (inside) {
+        // area_pixel_compute_source_index, align_corners=False: src = scale * (dst + 0.5) - 0.5, clamped at 0
+        float sy = p.scale_y * (oy + 0.5f) - 0.5f, sx = p.scale_x * (ox + 0.5f) - 0.5f;
+        sy = sy < 0.f ? 0.f : sy;
+        sx = sx < 0.f ? 0.f : sx;
+        const int y0 = (int)sy, x0 = (int)sx;
+        const int y1 = y0 + (y0 < p.H - 1 ? 1 : 0), x1 = x0 + (x0 < p.W - 1 ? 1 : 0);
+        const float ly1 = sy - y0, lx1 = sx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
+        float v00, v01, v10, v11;
+        if (BLUR) {
+            const float* tp = p.tmp + ((long long)b * p.C + c) * p.H * p.W;
+            v00 = v01 = v10 = v11 = 0.f;
+            for (int k = 0; k < p.ky; ++k) {
+                const long long ra = (long long)reflect_index(y0 + k - r, p.H) * p.W;
+                const long long rb = (long long)reflect_index(y1 + k - r, p.H) * p.W;
+                const float w = p.ty[k];
+                v00 = fmaf(w, tp[ra + x0], v00);
+                v01 = fmaf(w, tp[ra + x1], v01);
+                v10 = fmaf(w, tp[rb + x0], v10);
+                v11 = fmaf(w, tp[rb + x1], v11);
             }
-            v = ly0 * (lx0 * v00 + lx1 * v01) + ly1 * (lx0 * v10 + lx1 * v11);
+        } else {
+            v00 = load_src<U8>(p, b, c, y0, x0);
+            v01 = load_src<U8>(p, b, c, y0, x1);
+            v10 = load_src<U8>(p, b, c, y1, x0);
+            v11 = load_src<U8>(p, b, c, y1, x1);
         }
-        p.out[t] = v;
+        v = ly0 * (lx0 * v00 + lx1 * v01) + ly1 * (lx0 * v10 + lx1 * v11);
     }
+    p.out[(((long long)b * p.C + c) * p.pad_h + oy) * p.pad_w + ox] = v;
 }
 
 // same-size path (no resize): conversion + padding only
 template <bool U8>
 __global__ void __launch_bounds__(256) prep_copy_kernel(const __grid_constant__ PrepParams p) {
-    const long long total = (long long)p.B * p.C * p.pad_h * p.pad_w;
-    for (long long t = (long long)blockIdx.x * 256 + threadIdx.x; t < total; t += (long long)gridDim.x * 256) {
-        const int ox = (int)(t % p.pad_w);
-        long long q = t / p.pad_w;
-        const int oy = (int)(q % p.pad_h);
-        q /= p.pad_h;
-        const int c = (int)(q % p.C), b = (int)(q / p.C);
-        const bool inside = oy < p.out_h && ox < p.out_w;
-        if (p.mask != nullptr && c == 0) p.mask[((long long)b * p.pad_h + oy) * p.pad_w + ox] = inside ? 1 : 0;
-        p.out[t] = inside ? load_src<U8>(p, b, c, oy, ox) : 0.f;
-    }
+    const int ox = blockIdx.x * 256 + threadIdx.x, oy = blockIdx.y;
+    const int b = blockIdx.z / p.C, c = blockIdx.z - b * p.C;
+    if (ox >= p.pad_w) return;
+    const bool inside = oy < p.out_h && ox < p.out_w;
+    if (p.mask != nullptr && c == 0) p.mask[((long long)b * p.pad_h + oy) * p.pad_w + ox] = inside ? 1 : 0;
+    p.out[(((long long)b * p.C + c) * p.pad_h + oy) * p.pad_w + ox] = inside ? load_src<U8>(p, b, c, oy, ox) : 0.f;
 }
 
-static unsigned grid_for(long long total, int num_sms) {
-    const long long blocks = (total + 255) / 256;
-    const long long cap = (long long)num_sms * 16;  // grid-stride loop: a few resident waves
-    return (unsigned)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
-}
 
 int launch_prep_resize(const void* src, int src_kind, int B, int C, int H, int W, int out_h, int out_w, const float* taps_x,
                        int kx, const float* taps_y, int ky, float* tmp, float* out, int pad_h, int pad_w,
@@ -153,18 +135,19 @@ int launch_prep_resize(const void* src, int src_kind, int B, int C, int H, int W
         memcpy(p.ty, taps_y, sizeof(float) * ky);
     }
     const bool u8 = src_kind == 1;
-    const long long out_total = (long long)B * C * pad_h * pad_w;
+    B200_REQUIRE(H <= 65535 && pad_h <= 65535 && (long long)B * C <= 65535, "prep_resize: image or batch too large for the grid");
+    const dim3 g_src((W + 255) / 256, H, B * C), g_out((pad_w + 255) / 256, pad_h, B * C);
+    (void)num_sms;
     if (!blur && out_h == H && out_w == W) {
-        if (u8) prep_copy_kernel<true><<<grid_for(out_total, num_sms), 256, 0, stream>>>(p);
-        else prep_copy_kernel<false><<<grid_for(out_total, num_sms), 256, 0, stream>>>(p);
+        if (u8) prep_copy_kernel<true><<<g_out, 256, 0, stream>>>(p);
+        else prep_copy_kernel<false><<<g_out, 256, 0, stream>>>(p);
     } else if (blur) {
-        const long long src_total = (long long)B * C * H * W;
-        if (u8) prep_hblur_kernel<true><<<grid_for(src_total, num_sms), 256, 0, stream>>>(p);
-        else prep_hblur_kernel<false><<<grid_for(src_total, num_sms), 256, 0, stream>>>(p);
-        prep_resize_kernel<false, true><<<grid_for(out_total, num_sms), 256, 0, stream>>>(p);
+        if (u8) prep_hblur_kernel<true><<<g_src, 256, 0, stream>>>(p);
+        else prep_hblur_kernel<false><<<g_src, 256, 0, stream>>>(p);
+        prep_resize_kernel<false, true><<<g_out, 256, 0, stream>>>(p);
     } else {
-        if (u8) prep_resize_kernel<true, false><<<grid_for(out_total, num_sms), 256, 0, stream>>>(p);
-        else prep_resize_kernel<false, false><<<grid_for(out_total, num_sms), 256, 0, stream>>>(p);
+        if (u8) prep_resize_kernel<true, false><<<g_out, 256, 0, stream>>>(p);
+        else prep_resize_kernel<false, false><<<g_out, 256, 0, stream>>>(p);
     }
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;

@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(256) assign_combine_kernel(int M, int N, int t
 
 // pass 2: write the scores; ARGMAX also tracks per-tile row / column maxima (lowest index wins ties)
 template <bool ARGMAX>
-__global__ void __launch_bounds__(256) assign_finalize_kernel(const float* __restrict__ sim, float simw, int M, int N,
+__global__ void __launch_bounds__(256, ARGMAX ? 3 : 2) assign_finalize_kernel(const float* __restrict__ sim, float simw, int M, int N,
                                                               AssignWs w, float* __restrict__ scores,
                                                               const int* __restrict__ live) {
     __shared__ float tile[ARGMAX ? kAHalf * kAStride : 1];
