@@ -6,6 +6,7 @@ libb200glue.so.  All wrappers enqueue on torch's current CUDA stream and never s
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -353,22 +354,37 @@ def nn_match(sim, ratio_thresh, distance_thresh, mutual_check):
     return la, m0, m1, ms0, ms1
 
 
-def sg_sinkhorn_assignment(cost, bin_score, iters, threshold):
+# Pairs per Sinkhorn launch, 0 = one launch for the whole batch (default).  Measured (32 pairs x 2049^2 x 100 iterations,
+# scripts/bench_superglue.py): waves of 8 / 6 pairs, whose couplings (134 / 100 MB) stay in the 126 MB L2 across the
+# iterations, take 24.8 / 24.7 ms against 24.9 ms for one launch, waves of 4 / 3 / 2 pairs 34.5 / 50.6 / 58.5 ms (too few
+# row blocks per SM, one grid barrier per iteration and wave): the kernel is bound by its exponentials and issue slots
+# (ncu: alu 40 %, issue 56 %, dram 18 %), not by HBM, so L2 residency buys nothing.
+SINKHORN_WAVE = int(os.environ.get("B200GLUE_SINKHORN_WAVE", "0"))
+
+
+def sg_sinkhorn_assignment(cost, bin_score, iters, threshold, wave=None):
     """log_optimal_transport + mutual-NN filter: (scores [B,M+1,N+1], m0, m1, ms0, ms1)."""
     _require_cuda(cost, bin_score)
     b, m, n = cost.shape
     dev = cost.device
-    ws = torch.empty(_lib.lib().b200_sg_sinkhorn_workspace(b, m, n), dtype=torch.uint8, device=dev)
+    wave = SINKHORN_WAVE if wave is None else wave
+    if wave <= 0 or (m + 1) * (n + 1) * 4 * wave > 96 << 20:  # problems too large for L2 anyway: one launch
+        wave = b
+    wave = max(1, min(wave, b))
+    ws = torch.empty(_lib.lib().b200_sg_sinkhorn_workspace(wave, m, n), dtype=torch.uint8, device=dev)
     scores = torch.empty(b, m + 1, n + 1, dtype=torch.float32, device=dev)
     m0 = torch.empty(b, m, dtype=torch.int64, device=dev)
     m1 = torch.empty(b, n, dtype=torch.int64, device=dev)
     ms0 = torch.empty(b, m, dtype=torch.float32, device=dev)
     ms1 = torch.empty(b, n, dtype=torch.float32, device=dev)
     # algorithmic bytes: one pass over the couplings per iteration (+ the final write)
-    with _timed("sg_sinkhorn", 4, 4.0 * b * (m + 1) * (n + 1) * (iters + 2)):
-        _lib.check(_lib.lib().b200_sg_sinkhorn_assignment(_ptr(cost), _ptr(bin_score), b, m, n, int(iters), float(threshold),
-                                                          _ptr(ws), _ptr(scores), _ptr(m0), _ptr(m1), _ptr(ms0),
-                                                          _ptr(ms1), _stream()))
+    with _timed("sg_sinkhorn", 4 * ((b + wave - 1) // wave), 4.0 * b * (m + 1) * (n + 1) * (iters + 2)):
+        for b0 in range(0, b, wave):
+            nb = min(wave, b - b0)
+            _lib.check(_lib.lib().b200_sg_sinkhorn_assignment(
+                _ptr(cost, b0 * m * n), _ptr(bin_score), nb, m, n, int(iters), float(threshold), _ptr(ws),
+                _ptr(scores, b0 * (m + 1) * (n + 1)), _ptr(m0, b0 * m), _ptr(m1, b0 * n), _ptr(ms0, b0 * m),
+                _ptr(ms1, b0 * n), _stream()))
     return scores, m0, m1, ms0, ms1
 
 
