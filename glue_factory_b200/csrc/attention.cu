@@ -86,6 +86,10 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 #ifndef ATT_P_STORE8
 #define ATT_P_STORE8 1
 #endif
+// lazy rescale: the reference maximum moves only when a row's new maximum exceeds it by more than 2^ATT_LAZY_LOG2
+#ifndef ATT_LAZY_LOG2
+#define ATT_LAZY_LOG2 8
+#endif
 __device__ __forceinline__ void ex2_poly2(f32x2 x, float& e0, float& e1) {
     float x0, x1;
     upk2(x, x0, x1);
@@ -313,7 +317,7 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 }
                 const float m_tile = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
                 // lazy rescale: move the reference maximum only when it is off by more than 2^8
-                const bool need = (m_tile - m_run) * c > 8.0f;  // always true for n == 0 (m_run = -inf)
+                const bool need = (m_tile - m_run) * c > (float)ATT_LAZY_LOG2;  // always true for n == 0 (m_run = -inf)
                 if (n == 0) {
                     m_run = m_tile;
                 } else if (__any_sync(0xffffffffu, need)) {

@@ -106,39 +106,39 @@ class ImagePreprocessor:
         return self(torch.from_numpy(np.ascontiguousarray(read_image(image_path))).to(device))
 
     def get_new_image_size(self, h: int, w: int):
-        """(image.py:72-99)"""
-        side = self.conf.side
-        if isinstance(self.conf.resize, collections.Iterable):
-            assert len(self.conf.resize) == 2
-            return tuple(self.conf.resize)
-        side_size = self.conf.resize
-        aspect_ratio = w / h
-        if side not in ("short", "long", "vert", "horz"):
-            raise ValueError(f"side can be one of 'short', 'long', 'vert', and 'horz'. Got '{side}'")
-        if side == "vert":
-            size = side_size, int(side_size * aspect_ratio)
-        elif side == "horz":
-            size = int(side_size / aspect_ratio), side_size
-        elif (side == "short") ^ (aspect_ratio < 1.0):
-            size = side_size, int(side_size * aspect_ratio)
-        else:
-            size = int(side_size / aspect_ratio), side_size
-        if self.conf.edge_divisible_by is not None:
-            df = self.conf.edge_divisible_by
-            size = [int(x // df * df) for x in size]
-        return size
+        """Target (height, width) for an h x w image (image.py:72-99): an explicit pair wins; otherwise `resize` is the
+        length of the side named by `side`, the other side follows the aspect ratio (truncated), and both are rounded
+        down to a multiple of `edge_divisible_by`."""
+        target = self.conf.resize
+        if isinstance(target, collections.Iterable):
+            assert len(target) == 2
+            return tuple(target)
+        out = _fit_side(int(target), h, w, self.conf.side)
+        step = self.conf.edge_divisible_by
+        return out if step is None else [int(v // step * step) for v in out]
+
+
+def _fit_side(length: int, h: int, w: int, side: str):
+    """(height, width) with the chosen side equal to `length` (kornia's `side` convention: short / long / vert / horz)."""
+    if side not in ("short", "long", "vert", "horz"):
+        raise ValueError(f"side can be one of 'short', 'long', 'vert', and 'horz'. Got '{side}'")
+    ratio = w / h
+    if side in ("short", "long"):  # which axis is the short / long one decides; a square image counts as landscape
+        side = "vert" if (side == "short") != (ratio < 1.0) else "horz"
+    return (length, int(length * ratio)) if side == "vert" else (int(length / ratio), length)
 
 
 def read_image(path: Path, grayscale: bool = False) -> np.ndarray:
     """Read an image from path as RGB or grayscale (image.py:102-113)."""
     import cv2
 
-    if not Path(path).exists():
+    path = Path(path)
+    if not path.exists():
         raise FileNotFoundError(f"No image at path {path}.")
-    image = cv2.imread(str(path), cv2.IMREAD_GRAYSCALE if grayscale else cv2.IMREAD_COLOR)
-    if image is None:
+    pixels = cv2.imread(str(path), cv2.IMREAD_GRAYSCALE if grayscale else cv2.IMREAD_COLOR)
+    if pixels is None:
         raise IOError(f"Could not read image at {path}.")
-    return image if grayscale else image[..., ::-1]
+    return pixels if grayscale else pixels[..., ::-1]  # BGR -> RGB
 
 
 def numpy_image_to_torch(image: np.ndarray) -> torch.Tensor:

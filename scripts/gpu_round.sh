@@ -9,6 +9,7 @@ tail -n 3 gpurun_out/pytest_zz_$TAG.log
 timeout 1500 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/pytest_full_$TAG.log 2>&1; echo "full suite exit=$?"
 grep -E "passed|failed|error" gpurun_out/pytest_full_$TAG.log | tail -n 5
 grep -E "^(FAILED|ERROR)" gpurun_out/pytest_full_$TAG.log | head -n 20
+timeout 300 python __graft_entry__.py smoke 2>&1 | tail -n 2
 timeout 900 python bench.py "$@" > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err; echo "bench exit=$?"; tail -n 5 gpurun_out/bench_$TAG.err
 python - <<PY
 import json
