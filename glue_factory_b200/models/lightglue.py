@@ -100,6 +100,20 @@ def _split_b(w):
     return torch.cat([hi, lo, hi], 1).contiguous()
 
 
+def _fold_out_proj(w1, b1, wo, bo):
+    """cat[x, out_proj(ctx)] . W1^T + b1  ==  cat[x, ctx] . [W1a | W1b Wo]^T + (b1 + W1b bo): the message projection
+    (out_proj / to_out, lightglue.py:155,211-212) is a linear map feeding the first FFN layer (:138-143,157) with nothing
+    in between, so the two weights are multiplied once at packing time (fp64 product, one bf16 rounding) and the
+    256 x 256 GEMM per block disappears from the forward pass."""
+    w1, wo = w1.detach().double(), wo.detach().double()
+    d = wo.shape[0]
+    w = torch.cat([w1[:, :d], w1[:, d:] @ wo], 1)
+    b = b1.detach().double() + w1[:, d:] @ bo.detach().double()
+    return _bf16(w.float()), _f32(b.float())
+
+
+# B200GLUE_FOLD_OUT_PROJ=0 keeps out_proj / to_out as their own GEMMs (A/B measurement)
+FOLD_OUT_PROJ = os.environ.get("B200GLUE_FOLD_OUT_PROJ", "1") != "0"
 # B200GLUE_ASSIGN_BF16=1: plain bf16 final projection / similarity (A/B measurement of the fp32-grade path)
 ASSIGN_BF16 = os.environ.get("B200GLUE_ASSIGN_BF16", "0") == "1"
 
@@ -195,6 +209,11 @@ class LightGlue(nn.Module):
                 c_be=_f32(ca.ffn[1].bias), c_eps=float(ca.ffn[1].eps), c_w2=_bf16(ca.ffn[3].weight),
                 c_b2=_f32(ca.ffn[3].bias),
             ))
+            if FOLD_OUT_PROJ:
+                L[-1]["s_w1"], L[-1]["s_b1"] = _fold_out_proj(sa.ffn[0].weight, sa.ffn[0].bias, sa.out_proj.weight,
+                                                             sa.out_proj.bias)
+                L[-1]["c_w1"], L[-1]["c_b1"] = _fold_out_proj(ca.ffn[0].weight, ca.ffn[0].bias, ca.to_out.weight,
+                                                             ca.to_out.bias)
         A = []
         for a in self.log_assignment:
             s = float(a.dim) ** -0.25  # 0.25 for dim 256: folded into the projection (exact power of two)
@@ -222,20 +241,26 @@ class LightGlue(nn.Module):
         # self attention (lightglue.py:144-157)
         ops.gemm(ws["xm"], P["wqkv"], M=T, N=768, K=256, lda=512, block_n=256, epilogue=ops.EPI_QKV_ROTARY,
                  bias=P["bqkv"], cossin=ws["cs"], rot_cols=512, out16=ws["qkv"], ld16=768, tile_live=tl)
+        # with the message projection folded into the FFN weights the attention writes its context straight into the
+        # right half of XM = cat[x, .]
+        fold = FOLD_OUT_PROJ
+        ctx, ld_ctx, col_ctx = (ws["xm"], 512, 256) if fold else (ws["ctx"], 256, 0)
         ops.attention(ws["qkv"], ws["qkv"], ws["qkv"], seqs_self, num_seqs=nseq, max_q_len=max_len, heads=4,
-                      ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=ws["ctx"],
-                      ld_out=256, attn_work=work_self, len_override=lens)
-        ops.gemm(ws["ctx"], P["wo"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
-                 bias=P["bo"], out16=ws["xm"], out16_col0=256, ld16=512, tile_live=tl)
+                      ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=ctx,
+                      ld_out=ld_ctx, out_col0=col_ctx, attn_work=work_self, len_override=lens)
+        if not fold:
+            ops.gemm(ws["ctx"], P["wo"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
+                     bias=P["bo"], out16=ws["xm"], out16_col0=256, ld16=512, tile_live=tl)
         self._ffn_block(ws, T, P["s_w1"], P["s_b1"], P["s_g"], P["s_be"], P["s_eps"], P["s_w2"], P["s_b2"], tl)
         # bidirectional cross attention (lightglue.py:186-215)
         ops.gemm(ws["xm"], P["wc"], M=T, N=512, K=256, lda=512, block_n=256, epilogue=ops.EPI_BIAS_BF16,
                  bias=P["bc"], out16=ws["qkv"], ld16=768, tile_live=tl)
         ops.attention(ws["qkv"], ws["qkv"], ws["qkv"], seqs_cross, num_seqs=nseq, max_q_len=max_len, heads=4,
-                      ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=0, v_col0=256, scale=0.125, out=ws["ctx"],
-                      ld_out=256, attn_work=work_cross, len_override=lens)
-        ops.gemm(ws["ctx"], P["wco"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
-                 bias=P["bco"], out16=ws["xm"], out16_col0=256, ld16=512, tile_live=tl)
+                      ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=0, v_col0=256, scale=0.125, out=ctx,
+                      ld_out=ld_ctx, out_col0=col_ctx, attn_work=work_cross, len_override=lens)
+        if not fold:
+            ops.gemm(ws["ctx"], P["wco"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16,
+                     bias=P["bco"], out16=ws["xm"], out16_col0=256, ld16=512, tile_live=tl)
         self._ffn_block(ws, T, P["c_w1"], P["c_b1"], P["c_g"], P["c_be"], P["c_eps"], P["c_w2"], P["c_b2"], tl)
 
     def _project(self, A, ws, T, tile_live=None):

@@ -143,8 +143,13 @@ class SuperGlue(BaseModel):
             wm, bm = _fold(a.merge)
             w0, b0 = _fold(layer.mlp[0], layer.mlp[1])
             w3, b3 = _fold(layer.mlp[3])
-            L.append(dict(wqkv=_bf16(wq), bqkv=bq.contiguous(), wm=_bf16(wm[:, perm]), bm=bm, w0=_bf16(w0), b0=b0,
-                          w3=_bf16(w3), b3=b3))
+            # the merge convolution feeds the first MLP layer directly (superglue.py:131-140: mlp(cat[x, merge(ctx)])):
+            # the two linear maps are multiplied once here (fp64 product, one bf16 rounding), so the forward pass
+            # has no merge GEMM and the attention writes its context straight into the right half of cat[x, .]
+            w0d, wmd = w0.double(), wm[:, perm].double()
+            w0 = torch.cat([w0d[:, :256], w0d[:, 256:] @ wmd], 1).float()
+            b0 = (b0.double() + w0d[:, 256:] @ bm.double()).float().contiguous()
+            L.append(dict(wqkv=_bf16(wq), bqkv=bq.contiguous(), w0=_bf16(w0), b0=b0, w3=_bf16(w3), b3=b3))
         P["layers"] = L
         w, P["f_b"] = _fold(self.final_proj)
         P["f_w"] = _bf16(w)
@@ -212,10 +217,8 @@ class SuperGlue(BaseModel):
             ops.gemm(xm, Lw["wqkv"], M=T, N=768, K=256, lda=512, block_n=256, epilogue=ops.EPI_BIAS_BF16,
                      bias=Lw["bqkv"], out16=qkv, ld16=768)
             ops.attention(qkv, qkv, qkv, seqs_self if is_self else seqs_cross, num_seqs=2 * B, max_q_len=max(M, N),
-                          heads=4, ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=ctx,
-                          ld_out=256, attn_work=4.0 * 256 * B * ((M * M + N * N) if is_self else 2 * M * N))
-            ops.gemm(ctx, Lw["wm"], M=T, N=256, K=256, lda=256, block_n=256, epilogue=ops.EPI_BIAS_BF16, bias=Lw["bm"],
-                     out16=xm, out16_col0=256, ld16=512)
+                          heads=4, ldq=768, ldk=768, ldv=768, q_col0=0, k_col0=256, v_col0=512, scale=0.125, out=xm,
+                          ld_out=512, out_col0=256, attn_work=4.0 * 256 * B * ((M * M + N * N) if is_self else 2 * M * N))
             ops.gemm(xm, Lw["w0"], M=T, N=512, K=512, lda=512, block_n=256, epilogue=ops.EPI_BIAS_BF16, bias=Lw["b0"],
                      relu=1, out16=hbuf, ld16=512)
             ops.gemm(hbuf, Lw["w3"], M=T, N=256, K=512, lda=512, block_n=256, epilogue=ops.EPI_RESID, bias=Lw["b3"],
