@@ -30,8 +30,19 @@
 // The S matrix is never materialised in HBM.  Self-attention and both directions of the bidirectional
 // cross-attention use this kernel (the cross block's similarity is recomputed per direction).
 //
+// Two stream layouts share the code (template parameter WIDE):
+//   WIDE = false  item = 256 queries; stream = (query tile g of 2, key-tile parity x) as described above.  Twice as many,
+//                 half as long items: used when the wide layout would leave SMs without work (single pairs).
+//   WIDE = true   item = 512 queries; stream = query tile g of 4, every stream walks ALL key tiles of the item.  No merge,
+//                 no exchange between streams at all: a stream finishes its rows alone (O / l straight from its own
+//                 accumulator), K/V tiles are fetched once per 512 queries, and the per-item hand-over (the pair
+//                 barriers of the merge cost the narrow layout ~14 % of an item at 2048 keys) shrinks to the wait for
+//                 the stream's last PV.
+//
 // Replaces F.scaled_dot_product_attention / the einsum+softmax path of the reference
 // (reference: gluefactory/models/matchers/lightglue.py:105-122,144-157,186-215).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "attention.cuh"
 
@@ -39,14 +50,22 @@ namespace b200 {
 
 constexpr int kAttThreads = 544;
 constexpr int kQTile = 128, kKvTile = 64, kHeadDim = 64;
-constexpr int kQPerCta = 2 * kQTile;
 constexpr int kQBytes = kQTile * kHeadDim * 2;    // 16 KB
 constexpr int kKvBytes = kKvTile * kHeadDim * 2;  // 8 KB: 64 keys x 64 bf16
-constexpr int kKvStages = 8;
-constexpr int kXchFloats = 2 * 2 * 2 * kQTile;  // [m | l][query tile][stream parity][row]
-// smem: Q[query tile][2 buffers] | K[stages] V[stages] | barriers | (m, l) exchange
-constexpr int kAttSmemBytes = 1024 + 4 * kQBytes + 2 * kKvStages * kKvBytes + 512 + kXchFloats * 4;
-// stream s = 2 g + x:  S/P_s: [64 s, 64 s + 64)   O_s: [256 + 64 s, 256 + 64 s + 64)
+constexpr int kXchFloats = 2 * 2 * 2 * kQTile;  // narrow layout: [m | l][query tile][stream parity][row]
+template <bool WIDE>
+struct AttCfg {
+    static constexpr int kQTiles = WIDE ? 4 : 2;         // query tiles of an item
+    static constexpr int kQPerCta = kQTiles * kQTile;    // queries of an item
+    static constexpr int kKvStages = WIDE ? 6 : 8;       // wide: one K/V tile per round of the four streams (narrow: two)
+    static constexpr int kKvStride = WIDE ? 1 : 2;       // key tiles between two tiles of a stream
+    static constexpr int kKvUsers = WIDE ? 4 : 2;        // streams that consume one K/V tile
+    static constexpr int kQUsers = WIDE ? 1 : 2;         // streams that consume one Q tile
+    // smem: Q[query tile][2 buffers] | K[stages] V[stages] | barriers | (m, l) exchange (narrow only)
+    static constexpr int kSmemBytes = 1024 + 2 * kQTiles * kQBytes + 2 * kKvStages * kKvBytes + 512 + (WIDE ? 0 : kXchFloats * 4);
+};
+static_assert(AttCfg<true>::kSmemBytes <= 232448 && AttCfg<false>::kSmemBytes <= 232448, "attention smem");
+// stream s:  S/P_s: [64 s, 64 s + 64)   O_s: [256 + 64 s, 256 + 64 s + 64)
 constexpr uint32_t kAttTmemCols = 512;
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -83,6 +102,9 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
 #ifndef ATT_POLY_PAIRS
 #define ATT_POLY_PAIRS 4
 #endif
+#ifndef ATT_ISSUER_SPREAD
+#define ATT_ISSUER_SPREAD 0
+#endif
 #ifndef ATT_P_STORE8
 #define ATT_P_STORE8 1
 #endif
@@ -109,8 +131,9 @@ __device__ __forceinline__ void ex2_poly2(f32x2 x, float& e0, float& e1) {
 // one work item, decoded identically by every warp (all fields warp-uniform)
 struct AttItem {
     bool active;     // the item's first query tile holds at least one row
-    bool g1_active;  // so does the second one
     int q_row0, kv_row0, q_len, kv_len, kv_tiles, qt, head;
+    int q_first;     // first query of the item inside its sequence
+    __device__ __forceinline__ bool tile_active(int g) const { return q_first + g * kQTile < q_len; }
 };
 
 // the four words of an item that come from memory (two dependent global loads: ~1500 clk when not hidden)
@@ -128,6 +151,7 @@ __device__ __forceinline__ AttRaw att_fetch(const AttnParams& p, int it) {
     return r;
 }
 
+template <bool WIDE>
 __device__ __forceinline__ AttItem att_decode(const AttnParams& p, int it, const AttRaw& r) {
     AttItem a;
     a.qt = it % p.q_tiles;
@@ -136,27 +160,31 @@ __device__ __forceinline__ AttItem att_decode(const AttnParams& p, int it, const
     a.kv_len = __shfl_sync(0xffffffffu, r.kv_len, 0);
     a.q_row0 = __shfl_sync(0xffffffffu, r.q_row0, 0);
     a.kv_row0 = __shfl_sync(0xffffffffu, r.kv_row0, 0);
-    a.active = a.qt * kQPerCta < a.q_len;
-    a.g1_active = a.qt * kQPerCta + kQTile < a.q_len;
+    a.q_first = a.qt * AttCfg<WIDE>::kQPerCta;
+    a.active = a.q_first < a.q_len;
     a.kv_tiles = (a.kv_len + kKvTile - 1) / kKvTile;
     return a;
 }
 
-__device__ __forceinline__ AttItem att_item(const AttnParams& p, int it) { return att_decode(p, it, att_fetch(p, it)); }
+template <bool WIDE>
+__device__ __forceinline__ AttItem att_item(const AttnParams& p, int it) { return att_decode<WIDE>(p, it, att_fetch(p, it)); }
 
+template <bool WIDE>
 __global__ void __launch_bounds__(kAttThreads, 1)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                          const __grid_constant__ CUtensorMap tmap_v, const AttnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = align_smem_1024(smem_raw);
+    using Cfg = AttCfg<WIDE>;
+    constexpr int kQTiles = Cfg::kQTiles, kQPerCta = Cfg::kQPerCta, kKvStages = Cfg::kKvStages, kKvStride = Cfg::kKvStride;
     uint8_t* sQ = smem;  // [g][buffer]
-    uint8_t* sK = sQ + 4 * kQBytes;
+    uint8_t* sK = sQ + 2 * kQTiles * kQBytes;
     uint8_t* sV = sK + kKvStages * kKvBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kKvStages * kKvBytes);
     uint64_t* q_full = bars;                   // [g * 2 + buffer]
-    uint64_t* q_empty = q_full + 4;            // [g * 2 + buffer], one arrival per stream of the query tile
-    uint64_t* kv_full = q_empty + 4;           // [kKvStages]
-    uint64_t* kv_empty = kv_full + kKvStages;  // [kKvStages], one arrival per query tile
+    uint64_t* q_empty = q_full + 2 * kQTiles;  // [g * 2 + buffer], one arrival per stream of the query tile
+    uint64_t* kv_full = q_empty + 2 * kQTiles; // [kKvStages]
+    uint64_t* kv_empty = kv_full + kKvStages;  // [kKvStages], one arrival per stream that reads the tile
     uint64_t* s_full = kv_empty + kKvStages;   // [4]
     uint64_t* p_ready = s_full + 4;            // [4]
     uint64_t* o_done = p_ready + 4;            // [4]
@@ -172,16 +200,18 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         prefetch_tensormap(&tmap_q);
         prefetch_tensormap(&tmap_k);
         prefetch_tensormap(&tmap_v);
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < 2 * kQTiles; ++i) {
             mbar_init(q_full + i, 1);
-            mbar_init(q_empty + i, 2);
+            mbar_init(q_empty + i, Cfg::kQUsers);
+        }
+        for (int i = 0; i < 4; ++i) {
             mbar_init(s_full + i, 1);
             mbar_init(p_ready + i, 4);  // one arrival per warp of the stream
             mbar_init(o_done + i, 1);
         }
         for (int s = 0; s < kKvStages; ++s) {
             mbar_init(kv_full + s, 1);
-            mbar_init(kv_empty + s, 2);
+            mbar_init(kv_empty + s, Cfg::kKvUsers);
         }
         fence_barrier_init();
     }
@@ -195,15 +225,17 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         // ===================== TMA producer =====================
         const bool leader = elect_one();
         int kv_idx = 0;          // K/V tiles loaded so far (ring position)
-        int qcnt[2] = {0, 0};    // Q tiles loaded so far per query tile (buffer = count & 1)
+        int qcnt[kQTiles];       // Q tiles loaded so far per query tile (buffer = count & 1)
+#pragma unroll
+        for (int g = 0; g < kQTiles; ++g) qcnt[g] = 0;
         for (int it = blockIdx.x; it < p.num_items; it += gridDim.x) {
-            const AttItem a = att_item(p, it);
+            const AttItem a = att_item<WIDE>(p, it);
             if (!a.active || a.kv_tiles == 0) continue;
             const int col = a.head * kHeadDim;
-            const int qrow = a.q_row0 + a.qt * kQPerCta;
+            const int qrow = a.q_row0 + a.q_first;
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {
-                if (g == 1 && !a.g1_active) continue;
+            for (int g = 0; g < kQTiles; ++g) {
+                if (!a.tile_active(g)) continue;
                 const int slot = g * 2 + (qcnt[g] & 1);
                 mbar_wait(q_empty + slot, (uint32_t)(((qcnt[g] >> 1) & 1) ^ 1));
                 if (leader) {
@@ -228,34 +260,48 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     } else {
         // ============ stream (g, x): softmax + MMA issue + output, thread <-> query row ============
         const int s = (warp - 1) >> 2;
+#if ATT_ISSUER_SPREAD
+        const bool issuer = (warp & 3) == s;        // the issuers of the four streams sit on four different schedulers
+#else
         const bool issuer = ((warp - 1) & 3) == 0;  // first warp of the stream issues its MMAs
-        const int g = s >> 1, x = s & 1;
+#endif
+        const int g = WIDE ? s : s >> 1, x = WIDE ? 0 : s & 1;
         const int quarter = warp & 3;         // TMEM lane quarter this warp may touch
         const int row = quarter * 32 + lane;  // row inside the query tile == TMEM lane
         const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
         const uint32_t tmem_s = tmem_base + s * 64 + lane_off;
         const uint32_t tmem_o = tmem_base + 256 + s * 64 + lane_off;
-        const uint32_t tmem_o_other = tmem_base + 256 + (s ^ 1) * 64 + lane_off;
-        const int pair_bar = 1 + g * 4 + quarter;  // named barrier shared by the row's two streams
+        const uint32_t tmem_o_other = tmem_base + 256 + (s ^ 1) * 64 + lane_off;  // narrow layout only
+        const int pair_bar = 1 + g * 4 + quarter;  // named barrier shared by the row's two streams (narrow layout)
         constexpr uint32_t idesc_s = umma_idesc(128, 64, 1u, 0u, 0u);  // Q, K both K-major
         constexpr uint32_t idesc_o = umma_idesc(128, 64, 1u, 0u, 1u);  // P K-major (TMEM), V MN-major
         const bool lead_lane = elect_one();
         const float c = p.scale * 1.4426950408889634f;  // softmax(scale * s) via exp2
-        // S_s = Q_g K^T for ring tile `idx` with Q buffer `qslot`; whole warp calls, one lane issues
-        auto issue_s = [&](int idx, int qslot) {
-            const int stage = idx % kKvStages;
-            mbar_wait(kv_full + stage, (uint32_t)((idx / kKvStages) & 1));
+        // Operand descriptors: every tile base is 1024-aligned and all of shared memory lies below 256 KB, so the
+        // 14-bit address field of a descriptor advances linearly: descriptor(base + d) = descriptor(base) + (d >> 4).
+        // Building them from scratch (add, shift, mask, or - per MMA) put ~120 dependent uniform-datapath
+        // instructions between "P is ready" and the stream's next S, i.e. on the one path the stream waits for.
+        const uint64_t kdesc0 = umma_smem_desc_sw128(smem_u32(sK), 1024, 16);    // K tile, K-major
+        const uint64_t vdesc0 = umma_smem_desc_sw128(smem_u32(sV), 1024, 1024);  // V tile, MN-major (token-major)
+        const uint64_t qdesc0 = umma_smem_desc_sw128(smem_u32(sQ), 1024, 16);
+        constexpr uint32_t kKvDescStep = kKvBytes >> 4, kQDescStep = kQBytes >> 4;
+        // high word of the three descriptors (SBO 1024, version, swizzle; LBO lives in bits [16,30) of the low word and
+        // is ignored for swizzled K-major tiles / equals 1024 >> 4 = 64 for the MN-major V tile, carried by the low word)
+        const uint64_t desc_hi = kdesc0 & 0xffffffff00000000ull;
+        // S_s = Q_g K^T for the K tile in ring slot `stage` with Q buffer `qslot`; whole warp calls, one lane issues
+        auto issue_s_at = [&](int stage, uint32_t phase, int qslot) {
+            mbar_wait(kv_full + stage, phase);
             tc_fence_after();
-            const uint32_t aq = smem_u32(sQ + qslot * kQBytes), bk = smem_u32(sK + stage * kKvBytes);
             if (lead_lane) {
+                const uint64_t aq = qdesc0 + (uint32_t)qslot * kQDescStep, bk = kdesc0 + (uint32_t)stage * kKvDescStep;
 #pragma unroll
                 for (int k = 0; k < kHeadDim / 16; ++k)
-                    umma_f16(tmem_base + s * 64, umma_smem_desc_sw128(aq + k * 32, 1024, 16),
-                             umma_smem_desc_sw128(bk + k * 32, 1024, 16), idesc_s, k != 0 ? 1u : 0u);
+                    umma_f16(tmem_base + s * 64, aq + k * 2, bk + k * 2, idesc_s, k != 0 ? 1u : 0u);
                 umma_commit(s_full + s);
             }
             __syncwarp();
         };
+        auto issue_s = [&](int idx, int qslot) { issue_s_at(idx % kKvStages, (uint32_t)((idx / kKvStages) & 1), qslot); };
         int kv_base = 0;   // ring position of the current item's first K/V tile
         int qcnt = 0;      // Q tiles of query tile g used so far (buffer = count & 1)
         int n_tot = 0;     // key tiles this stream has processed so far (phase of s_full / p_ready)
@@ -271,12 +317,12 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
         for (int it = blockIdx.x; it < p.num_items; it += gridDim.x) {
             if (it != (int)blockIdx.x) raw = next_fetched ? raw_next : att_fetch(p, it);
             next_fetched = false;
-            const AttItem a = att_decode(p, it, raw);
+            const AttItem a = att_decode<WIDE>(p, it, raw);
             if (!a.active) continue;
-            if (g == 1 && !a.g1_active) {
-                // query tile without rows: only hand the K/V tiles of this stream's parity back to the producer
+            if (!a.tile_active(g)) {
+                // query tile without rows: only hand the K/V tiles of this stream back to the producer
                 if (issuer) {
-                    for (int t = x; t < a.kv_tiles; t += 2) {
+                    for (int t = x; t < a.kv_tiles; t += kKvStride) {
                         const int idx = kv_base + t;
                         mbar_wait(kv_full + idx % kKvStages, (uint32_t)((idx / kKvStages) & 1));
                         if (lane == 0) mbar_arrive(kv_empty + idx % kKvStages);
@@ -295,9 +341,12 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 issue_s(kv_base + x, qslot);
             }
             pre = false;
+            // ring slot of the stream's current tile, advanced incrementally (issuer only; no division in the key loop)
+            int stage = (kv_base + x) % kKvStages;
+            uint32_t phase = (uint32_t)(((kv_base + x) / kKvStages) & 1);
             float m_run = -INFINITY, l_run = 0.f;
             int n = 0;  // tiles of this stream in this item
-            for (int t = x; t < a.kv_tiles; t += 2, ++n, ++n_tot) {
+            for (int t = x; t < a.kv_tiles; t += kKvStride, ++n, ++n_tot) {
                 const int valid = min(kKvTile, a.kv_len - t * kKvTile);
                 mbar_wait(s_full + s, (uint32_t)(n_tot & 1));  // S_s(t) landed; every earlier MMA of the stream retired
                 tc_fence_after();
@@ -379,31 +428,51 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                     next_fetched = true;
                 }
                 if (issuer) {
+                    // Everything PV(t) and S(t + stride) need is prepared BEFORE the wait for P, the next K tile's
+                    // arrival included (it landed long ago: the ring runs several tiles ahead), so that only the
+                    // eight MMAs and their commits sit between "P is ready" and the stream's next S.
+                    const bool last = t + kKvStride >= a.kv_tiles;
+                    int nstage = stage + kKvStride;
+                    uint32_t nphase = phase;
+                    if (nstage >= kKvStages) {
+                        nstage -= kKvStages;
+                        nphase ^= 1u;
+                    }
+                    const uint64_t bv = vdesc0 + (uint32_t)stage * kKvDescStep;
+                    const uint64_t bk = kdesc0 + (uint32_t)nstage * kKvDescStep;
+                    const uint64_t aq = qdesc0 + (uint32_t)qslot * kQDescStep;
+                    if (!last) mbar_wait(kv_full + nstage, nphase);
+                    uint32_t bv_lo = (uint32_t)bv, bk_lo = (uint32_t)bk, aq_lo = (uint32_t)aq;
+                    uint32_t bar_kv = smem_u32(kv_empty + stage);
+                    asm volatile("" : "+r"(bv_lo), "+r"(bk_lo), "+r"(aq_lo), "+r"(bar_kv));  // computed before the wait
                     mbar_wait(p_ready + s, (uint32_t)(n_tot & 1));  // the four warps' P rows are in TMEM
                     tc_fence_after();
-                    const int idx = kv_base + t;
-                    const int stage = idx % kKvStages;
-                    const uint32_t bv = smem_u32(sV + stage * kKvBytes);
-                    const bool last = t + 2 >= a.kv_tiles;
                     if (lead_lane) {
 #pragma unroll
                         for (int k = 0; k < kKvTile / 16; ++k)
                             umma_f16_ts(tmem_base + 256 + s * 64, tmem_base + s * 64 + k * 8,
-                                        umma_smem_desc_sw128(bv + k * 2048, 1024, 1024), idesc_o, (n | k) != 0 ? 1u : 0u);
-                        umma_commit(kv_empty + stage);  // K_t / V_t free once this query tile's MMAs on them retire
+                                        (desc_hi | bv_lo) + (uint64_t)(k * 128), idesc_o, (n | k) != 0 ? 1u : 0u);
+                        umma_commit_addr(bar_kv);  // K_t / V_t free once every stream's MMAs on them retire
                         if (last) {
                             umma_commit(o_done + s);
                             umma_commit(q_empty + qslot);  // this stream is done with the item's Q tile
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < kHeadDim / 16; ++k)  // in order behind PV: may overwrite P
+                                umma_f16(tmem_base + s * 64, (desc_hi | aq_lo) + (uint64_t)(k * 2),
+                                         (desc_hi | bk_lo) + (uint64_t)(k * 2), idesc_s, k != 0 ? 1u : 0u);
+                            umma_commit(s_full + s);
                         }
                     }
                     __syncwarp();
-                    if (!last) {
-                        issue_s(idx + 2, qslot);  // in order behind PV: may overwrite P
-                    } else if (it + (int)gridDim.x < p.num_items) {
+                    stage = nstage;
+                    phase = nphase;
+                    if (last && it + (int)gridDim.x < p.num_items) {
                         // the next item's first S goes in right behind this item's last PV, so its start-up
-                        // (Q / K arrival, first MMA) runs under the merge below
-                        const AttItem nx = att_decode(p, it + gridDim.x, next_fetched ? raw_next : att_fetch(p, it + gridDim.x));
-                        if (nx.active && (g == 0 || nx.g1_active) && nx.kv_tiles > x) {
+                        // (Q / K arrival, first MMA) runs under the output pass below
+                        const AttItem nx =
+                            att_decode<WIDE>(p, it + gridDim.x, next_fetched ? raw_next : att_fetch(p, it + gridDim.x));
+                        if (nx.active && nx.tile_active(g) && nx.kv_tiles > x) {
                             const int nslot = g * 2 + ((qcnt + 1) & 1);
                             mbar_wait(q_full + nslot, (uint32_t)(((qcnt + 1) >> 1) & 1));
                             issue_s(kv_base + a.kv_tiles + x, nslot);
@@ -416,61 +485,96 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
                 if (lane == 0) mbar_arrive(q_empty + qslot);
                 __syncwarp();
             }
-            // ---- merge the row's two streams: O = (wA O_A + wB O_B) / (wA l_A + wB l_B); this stream writes
-            //      output dimensions [32 x, 32 x + 32) ----
-            float* xm = xch + ((g * 2 + x) * kQTile + row);
-            float* xo = xch + ((g * 2 + (x ^ 1)) * kQTile + row);
-            xm[0] = m_run;
-            xm[4 * kQTile] = l_run;
-            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-            const float m_o = xo[0], l_o = xo[4 * kQTile];
-            const float m_all = fmaxf(m_run, m_o);
-            const float w_me = have ? ex2_approx((m_run - m_all) * c) : 0.f;
-            const float w_o = have_other ? ex2_approx((m_o - m_all) * c) : 0.f;
-            const float l_all = l_run * w_me + l_o * w_o;
-            const float inv = l_all > 0.f ? 1.0f / l_all : 0.f;  // no keys: zeros
-            const float f_me = w_me * inv, f_o = w_o * inv;
-            if (have) {
-                mbar_wait(o_done + s, (uint32_t)((x == 0 ? od_a : od_b) & 1));  // the stream's last PV has landed
-                tc_fence_after();
-            }
-            if (have_other) {
-                mbar_wait(o_done + (s ^ 1), (uint32_t)((x == 0 ? od_b : od_a) & 1));
-                tc_fence_after();
-            }
-            float o[32];
-            if (have) {
-                tmem_ld32(tmem_o + x * 32, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]) * f_me;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] = 0.f;
-            }
-            if (have_other) {
-                tmem_ld32(tmem_o_other + x * 32, r);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[i] = fmaf(__uint_as_float(r[i]), f_o, o[i]);
-            }
-            const int q_idx = a.qt * kQPerCta + g * kQTile + row;
-            if (q_idx < a.q_len) {
+            if constexpr (WIDE) {
+                // ---- the stream owns its rows: O / l straight from its accumulator, 32 output dimensions at a time ----
+                const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;  // no keys: zeros
+                if (have) {
+                    mbar_wait(o_done + s, (uint32_t)(od_a & 1));  // the stream's last PV has landed
+                    tc_fence_after();
+                }
+                const int q_idx = a.q_first + g * kQTile + row;
                 __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                     (long long)(a.q_row0 + q_idx) * p.ld_out + p.out_col0 + a.head * kHeadDim + x * 32;
+                                     (long long)(a.q_row0 + q_idx) * p.ld_out + p.out_col0 + a.head * kHeadDim;
+                if (have) {
 #pragma unroll
-                for (int i = 0; i < 32; i += 8)
-                    *reinterpret_cast<uint4*>(dst + i) =
-                        make_uint4(pack_bf16(o[i], o[i + 1]), pack_bf16(o[i + 2], o[i + 3]),
-                                   pack_bf16(o[i + 4], o[i + 5]), pack_bf16(o[i + 6], o[i + 7]));
+                    for (int half = 0; half < 2; ++half) {
+                        uint32_t rr[32];
+                        tmem_ld32(tmem_o + half * 32, rr);
+                        tmem_ld_wait();
+                        if (q_idx < a.q_len) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 8)
+                                *reinterpret_cast<uint4*>(dst + half * 32 + i) =
+                                    make_uint4(pack_bf16(__uint_as_float(rr[i]) * inv, __uint_as_float(rr[i + 1]) * inv),
+                                               pack_bf16(__uint_as_float(rr[i + 2]) * inv, __uint_as_float(rr[i + 3]) * inv),
+                                               pack_bf16(__uint_as_float(rr[i + 4]) * inv, __uint_as_float(rr[i + 5]) * inv),
+                                               pack_bf16(__uint_as_float(rr[i + 6]) * inv, __uint_as_float(rr[i + 7]) * inv));
+                        }
+                    }
+                } else if (q_idx < a.q_len) {
+#pragma unroll
+                    for (int i = 0; i < kHeadDim; i += 8) *reinterpret_cast<uint4*>(dst + i) = make_uint4(0u, 0u, 0u, 0u);
+                }
+                // the accumulator reads are ordered before the stream's next PV by the fence in front of the next
+                // p_ready arrival (every warp of the stream passes it before the issuer goes on)
+                tc_fence_before();
+            } else {
+                // ---- merge the row's two streams: O = (wA O_A + wB O_B) / (wA l_A + wB l_B); this stream writes
+                //      output dimensions [32 x, 32 x + 32) ----
+                float* xm = xch + ((g * 2 + x) * kQTile + row);
+                float* xo = xch + ((g * 2 + (x ^ 1)) * kQTile + row);
+                xm[0] = m_run;
+                xm[4 * kQTile] = l_run;
+                asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+                const float m_o = xo[0], l_o = xo[4 * kQTile];
+                const float m_all = fmaxf(m_run, m_o);
+                const float w_me = have ? ex2_approx((m_run - m_all) * c) : 0.f;
+                const float w_o = have_other ? ex2_approx((m_o - m_all) * c) : 0.f;
+                const float l_all = l_run * w_me + l_o * w_o;
+                const float inv = l_all > 0.f ? 1.0f / l_all : 0.f;  // no keys: zeros
+                const float f_me = w_me * inv, f_o = w_o * inv;
+                if (have) {
+                    mbar_wait(o_done + s, (uint32_t)((x == 0 ? od_a : od_b) & 1));  // the stream's last PV has landed
+                    tc_fence_after();
+                }
+                if (have_other) {
+                    mbar_wait(o_done + (s ^ 1), (uint32_t)((x == 0 ? od_b : od_a) & 1));
+                    tc_fence_after();
+                }
+                float o[32];
+                if (have) {
+                    tmem_ld32(tmem_o + x * 32, r);
+                    tmem_ld_wait();
+    #pragma unroll
+                    for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]) * f_me;
+                } else {
+    #pragma unroll
+                    for (int i = 0; i < 32; ++i) o[i] = 0.f;
+                }
+                if (have_other) {
+                    tmem_ld32(tmem_o_other + x * 32, r);
+                    tmem_ld_wait();
+    #pragma unroll
+                    for (int i = 0; i < 32; ++i) o[i] = fmaf(__uint_as_float(r[i]), f_o, o[i]);
+                }
+                const int q_idx = a.q_first + g * kQTile + row;
+                if (q_idx < a.q_len) {
+                    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) +
+                                         (long long)(a.q_row0 + q_idx) * p.ld_out + p.out_col0 + a.head * kHeadDim + x * 32;
+    #pragma unroll
+                    for (int i = 0; i < 32; i += 8)
+                        *reinterpret_cast<uint4*>(dst + i) =
+                            make_uint4(pack_bf16(o[i], o[i + 1]), pack_bf16(o[i + 2], o[i + 3]),
+                                       pack_bf16(o[i + 4], o[i + 5]), pack_bf16(o[i + 6], o[i + 7]));
+                }
+                tc_fence_before();
+                // both streams have read both accumulators (and the exchange slots): the next item may overwrite them
+                asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
             }
-            tc_fence_before();
-            // both streams have read both accumulators (and the exchange slots): the next item may overwrite them
-            asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
             kv_base += a.kv_tiles;
             if (has_q) ++qcnt;
             if (a.kv_tiles > 0) ++od_a;
-            if (a.kv_tiles > 1) ++od_b;
+            if (!WIDE && a.kv_tiles > 1) ++od_b;
         }
     }
     tc_fence_before();
@@ -478,24 +582,51 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     if (warp == 0) tmem_dealloc<kAttTmemCols>(tmem_base);
 }
 
-int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
-                     int num_seqs, int max_q_len, int heads, int num_sms, cudaStream_t stream) {
+// Layout choice: the wide layout wins ~10 % per item at full occupancy but makes half as many items; take it unless
+// the narrow layout fills the SMs noticeably better (whole waves of equal items: time ~ waves x item length).
+// B200GLUE_ATT_LAYOUT=wide|narrow forces one (experiments, tests).
+static int att_layout_override() {  // read per call (a getenv is nanoseconds): tests switch it inside one process
+    const char* e = getenv("B200GLUE_ATT_LAYOUT");
+    if (!e) return -1;
+    return e[0] == 'w' ? 1 : e[0] == 'n' ? 0 : -1;
+}
+
+template <bool WIDE>
+static int launch_attention_as(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
+                               long long items, int num_sms, cudaStream_t stream) {
     static PerDeviceSize configured;
     if (!configured.cur()) {
-        B200_CHECK_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             kAttSmemBytes));
+        B200_CHECK_CUDA(cudaFuncSetAttribute(attention_tcgen05_kernel<WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             AttCfg<WIDE>::kSmemBytes));
         configured.cur() = 1;
     }
-    if (num_seqs == 0 || max_q_len == 0) return 0;
-    p.q_tiles = (max_q_len + kQPerCta - 1) / kQPerCta;
-    p.heads = heads;
-    const long long items = (long long)p.q_tiles * heads * num_seqs;
-    B200_REQUIRE(items < (1ll << 31), "attention: too many work items");
     p.num_items = (int)items;
     const int grid = (int)(items < num_sms ? items : num_sms);
-    attention_tcgen05_kernel<<<grid, kAttThreads, kAttSmemBytes, stream>>>(tq, tk, tv, p);
+    attention_tcgen05_kernel<WIDE><<<grid, kAttThreads, AttCfg<WIDE>::kSmemBytes, stream>>>(tq, tk, tv, p);
     B200_CHECK_CUDA(cudaGetLastError());
     return 0;
+}
+
+int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
+                     int num_seqs, int max_q_len, int heads, int num_sms, cudaStream_t stream) {
+    if (num_seqs == 0 || max_q_len == 0) return 0;
+    p.heads = heads;
+    const int qt_n = (max_q_len + AttCfg<false>::kQPerCta - 1) / AttCfg<false>::kQPerCta;
+    const int qt_w = (max_q_len + AttCfg<true>::kQPerCta - 1) / AttCfg<true>::kQPerCta;
+    const long long items_n = (long long)qt_n * heads * num_seqs, items_w = (long long)qt_w * heads * num_seqs;
+    B200_REQUIRE(items_n < (1ll << 31), "attention: too many work items");
+    // relative time: waves x (item length in 128-query tiles), the wide item taken at kWideGain of two narrow ones
+    const double kWideGain = 0.92;
+    const double t_n = (double)((items_n + num_sms - 1) / num_sms) * 1.0;
+    const double t_w = (double)((items_w + num_sms - 1) / num_sms) * 2.0 * kWideGain;
+    bool wide = t_w <= t_n;
+    if (att_layout_override() >= 0) wide = att_layout_override() == 1;
+    if (wide) {
+        p.q_tiles = qt_w;
+        return launch_attention_as<true>(tq, tk, tv, p, items_w, num_sms, stream);
+    }
+    p.q_tiles = qt_n;
+    return launch_attention_as<false>(tq, tk, tv, p, items_n, num_sms, stream);
 }
 
 }  // namespace b200

@@ -245,6 +245,10 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
                      smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ void umma_commit_addr(uint32_t bar_smem_addr) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_smem_addr)
+                 : "memory");
+}
 // 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives row (lane base + i)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
