@@ -26,6 +26,7 @@ void set_last_error(const char* fmt, ...) {
     va_end(ap);
 }
 
+int ln_part_cols();
 int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const CUtensorMap& tb,
                 const GemmParams& p, int num_sms, cudaStream_t stream);
 int launch_conv_patch(int cout, const CUtensorMap& ta, const CUtensorMap& tw, const GemmParams& p, int num_sms,
@@ -215,7 +216,7 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
         if (make_map_2d(&tb, d->b, d->N, 576, 576, (uint32_t)d->N) != 0) return -1;
         return launch_conv_patch(d->N, ta, tb, p, num_sms, stream);
     }
-    const uint32_t b_box = d->block_n > 256 ? 256u : (uint32_t)d->block_n;
+    const uint32_t b_box = epi == EPI_LN_GELU ? (uint32_t)ln_part_cols() : d->block_n > 256 ? 256u : (uint32_t)d->block_n;
     if (make_map_2d(&tb, d->b, d->b_rows, d->K, d->ldb, b_box) != 0) return -1;
     int a_mode = 0;
     if (d->conv) {

@@ -15,6 +15,8 @@
 // Replaces the cuDNN / cuBLAS calls behind nn.Conv2d and nn.Linear on the reference path
 // (reference: gluefactory/models/extractors/superpoint_open.py:59-115,
 //  gluefactory/models/matchers/lightglue.py:125-215,265-281).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "gemm.cuh"
 
@@ -27,6 +29,7 @@ constexpr int kTileH = 8, kTileW = 16;  // conv M-tile: 8 x 16 pixels
 // LayerNorm + GELU epilogue, which is instruction-latency-bound per warp
 constexpr int kEpiWarps = 8;
 constexpr int kEpiWarpsLn = 16;
+constexpr int kLnPartDefault = 128;  // measured in the step: 1.807 ms (128) vs 1.873 ms (256) per 18 launches
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == EPI_LN_GELU ? kEpiWarpsLn : kEpiWarps; }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged in smem (bias | scale/gamma | shift/beta)
@@ -46,34 +49,39 @@ struct GemmCfg {
     // K = 256 tile in flight), three for the fp32-staged ones
     static constexpr int kRingBudget = 227 * 1024 - 1024 - 256 - epi_smem_bytes(EPI);
     static constexpr int kStages = (kRingBudget / kStageBytes) > 8 ? 8 : (kRingBudget / kStageBytes);
-    static constexpr int kAccStages = BLOCK_N <= 256 ? 2 : 1;
+    // LayerNorm epilogue: the 512-column row lives in TMEM as 512 / BLOCK_N accumulator stages (column parts)
+    static constexpr int kAccStages = EPI == EPI_LN_GELU ? 512 / BLOCK_N : (BLOCK_N <= 256 ? 2 : 1);
     static constexpr int kAccStride = BLOCK_N <= 64 ? 64 : (BLOCK_N <= 128 ? 128 : (BLOCK_N <= 256 ? 256 : 512));
     static constexpr int kTmemCols = kAccStride * kAccStages < 32 ? 32 : kAccStride * kAccStages;
     static constexpr int kUmmaN = BLOCK_N > 256 ? 256 : BLOCK_N;
     static constexpr int kNumUmmaN = BLOCK_N / kUmmaN;
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + epi_smem_bytes(EPI);
-    static_assert((2 * kStages + 2 * 2) * 8 + 8 <= 256, "barrier block");
+    static_assert((2 * kStages + 2 * kAccStages) * 8 + 8 <= 256, "barrier block");
     static_assert(kStageBytes % 1024 == 0, "stage must keep 1024-byte alignment for SWIZZLE_128B");
     static_assert(kTmemCols <= 512, "TMEM budget");
     static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
-// GELU(erf): 0.5 x (1 + erf(x / sqrt 2)) = hx + |hx| (1 - poly(t) exp(-x^2 / 2)), hx = x / 2, with the
-// Abramowitz-Stegun 7.1.26 form of erf (|error| <= 1.5e-7; measured against float64 over [-8, 8]: absolute
-// error of the GELU <= 5e-7, relative <= 8e-5 for x > -3).  11 FMA-pipe + 2 MUFU instructions instead of
-// the ~25 of erff (two-branch polynomial with selects): this epilogue is instruction-bound.
+// GELU(erf) = x Phi(x) = max(x, 0) - a Phi(-a), a = |x|, with Phi(-a) = 2^q(a): q is the degree-6 weighted minimax
+// fit of log2(erfc(a / sqrt 2) / 2) on [0, 6] (beyond 6, a is clamped: Phi(-6) = 1e-9).  Measured against float64
+// over [-9, 9] in fp32 arithmetic: absolute error <= 5.1e-7, relative <= 1e-5 for x > -3 (the Abramowitz-Stegun
+// 7.1.26 form used before: 5e-7 / 8e-5, with a reciprocal and an exponential per element).  ONE MUFU and 7 FMA-pipe
+// instructions per element instead of ~25 for erff: this epilogue is MUFU- and issue-bound.
+// The polynomial is evaluated in n = -a (odd coefficients change sign), so that the result is one FMA: n E + relu.
+constexpr float kGeluQ0 = -9.999930263e-01f, kGeluQ1 = 1.151201725e+00f, kGeluQ2 = -4.587708414e-01f,
+                kGeluQ3 = 5.341226608e-02f, kGeluQ4 = 8.080814034e-03f, kGeluQ5 = 7.692475338e-04f,
+                kGeluQ6 = 3.309584281e-05f;
 __device__ __forceinline__ float gelu_erf(float x) {
-    const float ax = fabsf(x);
-    float t, e;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.23164189f, 1.0f)));  // p / sqrt 2
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752f));          // exp(-x^2 / 2)
-    float poly = fmaf(t, 1.061405429f, -1.453152027f);
-    poly = fmaf(t, poly, 1.421413741f);
-    poly = fmaf(t, poly, -0.284496736f);
-    poly = fmaf(t, poly, 0.254829592f);
-    poly *= t;
-    const float hx = 0.5f * x;
-    return fmaf(fabsf(hx), fmaf(-poly, e, 1.0f), hx);
+    const float n = fmaxf(-fabsf(x), -6.0f);
+    float q = fmaf(n, kGeluQ6, kGeluQ5);
+    q = fmaf(q, n, kGeluQ4);
+    q = fmaf(q, n, kGeluQ3);
+    q = fmaf(q, n, kGeluQ2);
+    q = fmaf(q, n, kGeluQ1);
+    q = fmaf(q, n, kGeluQ0);
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(q));
+    return fmaf(n, e, fmaxf(x, 0.f));
 }
 
 // packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2 on sm_100: two fp32 operations per issue slot).  A pair lives in
@@ -102,27 +110,23 @@ __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
     return d;
 }
 
-// gelu_erf on two elements at once: 12 packed FMA-pipe instructions + 2 LOP + 4 MUFU per pair
+// gelu_erf on two elements at once: 4 FMNMX + 7 packed FMA-pipe instructions + 2 MUFU per pair
 __device__ __forceinline__ f32x2 gelu_erf2(f32x2 x) {
     float x0, x1;
     upk2(x, x0, x1);
-    const f32x2 ax = pk2(fabsf(x0), fabsf(x1));
-    float d0, d1, a0, a1, t0, t1, e0, e1;
-    upk2(fma2(ax, bc2(0.23164189f), bc2(1.0f)), d0, d1);
-    upk2(mul2(mul2(x, bc2(-0.72134752f)), x), a0, a1);
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
-    const f32x2 t = pk2(t0, t1), e = pk2(e0, e1);
-    // -poly(t): the coefficients carry the sign, so that 1 - poly e is one FMA
-    f32x2 np = fma2(t, bc2(-1.061405429f), bc2(1.453152027f));
-    np = fma2(t, np, bc2(-1.421413741f));
-    np = fma2(t, np, bc2(0.284496736f));
-    np = fma2(t, np, bc2(-0.254829592f));
-    np = mul2(np, t);
-    const f32x2 w = fma2(np, e, bc2(1.0f));
-    return fma2(mul2(ax, bc2(0.5f)), w, mul2(x, bc2(0.5f)));
+    const f32x2 n = pk2(fmaxf(-fabsf(x0), -6.0f), fmaxf(-fabsf(x1), -6.0f));
+    const f32x2 relu = pk2(fmaxf(x0, 0.f), fmaxf(x1, 0.f));
+    f32x2 q = fma2(n, bc2(kGeluQ6), bc2(kGeluQ5));
+    q = fma2(q, n, bc2(kGeluQ4));
+    q = fma2(q, n, bc2(kGeluQ3));
+    q = fma2(q, n, bc2(kGeluQ2));
+    q = fma2(q, n, bc2(kGeluQ1));
+    q = fma2(q, n, bc2(kGeluQ0));
+    float q0, q1, e0, e1;
+    upk2(q, q0, q1);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(q0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(q1));
+    return fma2(n, pk2(e0, e1), relu);
 }
 
 __device__ __forceinline__ void store16B(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -323,14 +327,15 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
 // Linear(512 -> 512) -> LayerNorm(512) -> GELU(erf).  The row is computed as two 256-column halves, one per
 // TMEM accumulator stage, so that the MMAs of the next row tile's first half run under the second half of this
 // epilogue (a single 128 x 512 fp32 accumulator would fill the TMEM and serialise MMA and epilogue).
-// `grp` (0..3) = this warp's column group inside a half: chunks grp and grp + 4 of the half's eight.
+// `grp` (0..3) = this warp's column group inside a part: 32-column chunks grp, grp + 4, ... of the part's PART_N / 32.
+template <int PART_N>
 __device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_taddr, int col_base, int grp,
                                               float& sum, float& sumsq) {
     uint32_t r[32];
     const uint32_t bias_s = smem_u32(es.bias);
     f32x2 sum2 = bc2(0.f), sq2 = bc2(0.f);
 #pragma unroll 1
-    for (int c = grp; c < 8; c += 4) {
+    for (int c = grp; c < PART_N / 32; c += 4) {
         tmem_ld32(half_taddr + c * 32, r);
         float4 b[8];
 #pragma unroll
@@ -351,6 +356,7 @@ __device__ __forceinline__ void ln_stats_half(const EpiSmem& es, uint32_t half_t
     sumsq += q0 + q1;
 }
 
+template <int PART_N>
 __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem& es, uint32_t half_taddr, int col_base,
                                              long long tile_row0, int grp, int lane, float rstd, float nmr) {
     uint32_t r[32];
@@ -358,7 +364,7 @@ __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem&
     const uint32_t stage = smem_u32(es.stage);
     const f32x2 rstd2 = bc2(rstd), nmr2 = bc2(nmr);
 #pragma unroll 1
-    for (int c = grp; c < 8; c += 4) {
+    for (int c = grp; c < PART_N / 32; c += 4) {
         tmem_ld32(half_taddr + c * 32, r);
         tmem_ld_wait();
         uint32_t pk[16];
@@ -556,7 +562,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
     const int m_tiles = A_MODE == 1 ? p.tiles_x * p.tiles_y : (p.M + kBlockM - 1) / kBlockM;
     // LayerNorm epilogue: a tile is a full 512-column row block, produced as kHalves column halves by the same CTA
-    constexpr int kHalves = EPI == EPI_LN_GELU ? 2 : 1;
+    constexpr int kHalves = EPI == EPI_LN_GELU ? 512 / BLOCK_N : 1;
     const int n_tiles = EPI == EPI_LN_GELU ? 1 : (p.N + BLOCK_N - 1) / BLOCK_N;
     const long long total_tiles = (long long)p.batch * m_tiles * n_tiles;
     const int k_blocks = p.K / kBlockK;
@@ -712,18 +718,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             const int nt = tc.nt, mt = tc.mt, b = tc.b;
             if (p.tile_live != nullptr && p.tile_live[b * m_tiles + mt] == 0) continue;
             if constexpr (EPI == EPI_LN_GELU) {
-                // accumulator stage h holds columns [256 h, 256 h + 256) of this row tile; both stages turn over once
-                // per tile, so one phase bit serves both.  `half` is this warp's column group (0..3) here.
-                static_assert(Cfg::kAccStages == 2 && Cfg::kAccStride == 256, "LayerNorm epilogue: two 256-column halves");
+                // accumulator stage h holds columns [BLOCK_N h, BLOCK_N (h + 1)) of this row tile; every stage turns over
+                // once per tile, so one phase bit serves all.  `half` is this warp's column group (0..3) here.
+                // Statistics of part h run under the MMAs of part h + 1; after the last part the row is normalised
+                // part by part and each part's accumulator is handed back as soon as it has been read, so the next
+                // tile's MMAs start under this tile's remaining parts.  Narrow parts (128 columns) shorten the one
+                // stretch nothing overlaps: last part's MMAs -> its statistics -> first part normalised.
+                static_assert(Cfg::kAccStages * BLOCK_N == 512 && Cfg::kAccStride == BLOCK_N, "LayerNorm epilogue: 512 columns");
                 const uint32_t lane_taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
                 const long long row0 = (long long)mt * kBlockM + quarter * 32;
                 float sum = 0.f, sumsq = 0.f;
-                mbar_wait(acc_full + 0, acc_phase);
-                tc_fence_after();
-                ln_stats_half(es, lane_taddr, 0, half, sum, sumsq);
-                mbar_wait(acc_full + 1, acc_phase);
-                tc_fence_after();
-                ln_stats_half(es, lane_taddr + 256, 256, half, sum, sumsq);
+#pragma unroll
+                for (int h = 0; h < Cfg::kAccStages; ++h) {
+                    mbar_wait(acc_full + h, acc_phase);
+                    tc_fence_after();
+                    ln_stats_half<BLOCK_N>(es, lane_taddr + h * BLOCK_N, h * BLOCK_N, half, sum, sumsq);
+                }
                 float2* exch = es.exch + (acc_phase & 1) * 512;
                 exch[half * 128 + r_in_tile] = make_float2(sum, sumsq);
                 epi_bar_sync<kEpiWarpsLn>();
@@ -737,14 +747,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 const float var = fmaxf(sumsq * (1.0f / 512.f) - mean * mean, 0.f);
                 const float rstd = rsqrtf(var + p.ln_eps);
                 const float nmr = -mean * rstd;
-                ln_gelu_half(p, es, lane_taddr, 0, row0, half, lane, rstd, nmr);
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(acc_empty + 0);  // the next tile's first half starts under our second half
-                ln_gelu_half(p, es, lane_taddr + 256, 256, row0, half, lane, rstd, nmr);
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(acc_empty + 1);
+#pragma unroll
+                for (int h = 0; h < Cfg::kAccStages; ++h) {
+                    ln_gelu_half<BLOCK_N>(p, es, lane_taddr + h * BLOCK_N, h * BLOCK_N, row0, half, lane, rstd, nmr);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_empty + h);
+                }
                 acc_phase ^= 1;
                 continue;
             }
@@ -783,6 +792,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 // ---------------------------------------------------------------------------------------------
 // host launcher
 // ---------------------------------------------------------------------------------------------
+// column width of an accumulator part of the LayerNorm epilogue (also the row count of the weight TMA box):
+// B200GLUE_LN_PART=128|256 for experiments
+int ln_part_cols() {
+    static const int v = [] {
+        const char* e = getenv("B200GLUE_LN_PART");
+        return (e != nullptr && atoi(e) == 256) ? 256 : (e != nullptr && atoi(e) == 128) ? 128 : kLnPartDefault;
+    }();
+    return v;
+}
+
 template <int BLOCK_N, int EPI, int A_MODE>
 static int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int num_sms,
                       cudaStream_t stream) {
@@ -810,8 +829,10 @@ int launch_gemm(int block_n, int epi, int a_mode, const CUtensorMap& ta, const C
     B200_CASE(128, EPI_BIAS_BF16, 0)
     B200_CASE(256, EPI_BIAS_BF16, 0)
     B200_CASE(256, EPI_QKV_ROTARY, 0)
-    if (block_n == 512 && epi == EPI_LN_GELU && a_mode == 0)  // 512 columns as two 256-column accumulator halves
+    if (block_n == 512 && epi == EPI_LN_GELU && a_mode == 0) {  // 512 columns as 128- or 256-column accumulator parts
+        if (ln_part_cols() == 128) return launch_one<128, EPI_LN_GELU, 0>(ta, tb, p, num_sms, stream);
         return launch_one<256, EPI_LN_GELU, 0>(ta, tb, p, num_sms, stream);
+    }
     B200_CASE(256, EPI_RESID, 0)
     B200_CASE(128, EPI_F32, 0)
     B200_CASE(256, EPI_F32, 0)
