@@ -14,7 +14,7 @@
 //
 //   warp 0: TMA producer (weights once, then one patch per tile through a ring)
 //   warp 1: TMEM allocation + single-thread tcgen05.mma issue (36 MMAs of 128 x C_out x 16 per tile)
-//   warps 2-5: epilogue: thread per pixel row: TMEM -> bias -> ReLU -> BN affine -> bf16 -> swizzled smem tile;
+//   warps 2-9: epilogue: thread per (pixel row, 32-column group): TMEM -> bias -> ReLU -> BN affine -> bf16 -> swizzled smem tile;
 //              then thread per (output pixel, 16 B): optional 2x2 max (bf16x2) and coalesced NHWC stores.
 //              The accumulator is double-buffered in TMEM so the epilogue overlaps the next tile's MMAs.
 //
@@ -28,7 +28,15 @@ namespace b200 {
 constexpr int kCpTileW = 8, kCpTileH = 16;
 constexpr int kCpPatchW = 16, kCpPatchH = kCpTileH + 2;
 constexpr int kCpPatchBytes = kCpPatchW * kCpPatchH * 128;  // 36 KB
-constexpr int kCpThreads = 192;
+// epilogue warps: the epilogue (TMEM -> bias / ReLU / BN -> bf16 -> staging -> pooled NHWC stores) of four warps took
+// ~2000 of a tile's ~2400 clk (ncu: they waited for the accumulator only 16 % of the time), i.e. it, not the MMAs, set
+// the pace; two warps per TMEM lane quarter split the columns.
+#ifndef CP_EPI_WARPS
+#define CP_EPI_WARPS 8
+#endif
+constexpr int kCpEpiWarps = CP_EPI_WARPS;
+constexpr int kCpEpiThreads = 32 * kCpEpiWarps;
+constexpr int kCpThreads = 64 + kCpEpiThreads;
 
 template <int COUT>
 struct ConvPatchCfg {
@@ -40,7 +48,7 @@ struct ConvPatchCfg {
     static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kCpEpiThreads) : "memory"); }
 __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
     uint32_t d;
     asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
@@ -100,7 +108,7 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(acc_full + s, 1);
-            mbar_init(acc_empty + s, 4);
+            mbar_init(acc_empty + s, kCpEpiWarps);
         }
         mbar_init(w_full, 1);
         fence_barrier_init();
@@ -131,7 +139,10 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
     } else if (warp == 1) {
         // whole warp walks the tile loop (uniform control flow); one elected lane issues the MMAs / commits
-        constexpr uint32_t idesc = umma_idesc(128, COUT, 1u, 0u, 0u);
+#ifndef CONV_TIMING_MMA_N  // timing experiments only (results are wrong for any value but COUT): B-operand read share
+#define CONV_TIMING_MMA_N COUT
+#endif
+        constexpr uint32_t idesc = umma_idesc(128, CONV_TIMING_MMA_N, 1u, 0u, 0u);
         mbar_wait(w_full, 0);
         int stage = 0, acc = 0;
         uint32_t phase = 0, acc_phase = 0;
@@ -161,15 +172,15 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     } else {
-        // ===================== epilogue (128 threads) =====================
+        // ===================== epilogue (kCpEpiThreads threads) =====================
         // phase A: thread <-> pixel row: TMEM -> bias/ReLU/BN -> bf16 -> swizzled staging tile in smem
         // phase B: thread <-> (output pixel, 16-byte chunks): optional 2x2 max, coalesced NHWC stores
-        const int quarter = warp & 3;
-        const int et = threadIdx.x - 64;  // 0..127
+        const int quarter = warp & 3, grp = (warp - 2) >> 2;  // TMEM lane quarter; column group of the warp
+        const int et = threadIdx.x - 64;  // 0 .. kCpEpiThreads - 1
         const int r_in_tile = quarter * 32 + lane;
         const bool pool = p.pool != 0;
         const int OH = pool ? (p.H >> 1) : p.H, OW = pool ? (p.W >> 1) : p.W;
-        for (int i = et; i < COUT; i += 128) {
+        for (int i = et; i < COUT; i += kCpEpiThreads) {
             sPar[i] = __ldg(p.bias + i);
             sPar[COUT + i] = __ldg(p.scale + i);
             sPar[2 * COUT + i] = __ldg(p.shift + i);
@@ -191,7 +202,7 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const uint32_t taddr = tmem_base + acc * COUT + ((uint32_t)(quarter * 32) << 16);
             uint8_t* my_row = sStage + r_in_tile * (COUT * 2);
 #pragma unroll
-            for (int c = 0; c < COUT / 32; ++c) {
+            for (int c = grp; c < COUT / 32; c += kCpEpiWarps / 4) {
                 tmem_ld32(taddr + c * 32, r);
                 tmem_ld_wait();
                 uint32_t pk[16];
@@ -219,7 +230,7 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             constexpr int kChunks = COUT / 8;  // 16-byte chunks per pixel
             if (pool) {
                 // 32 pooled pixels x kChunks chunks
-                for (int item = et; item < 32 * kChunks; item += 128) {
+                for (int item = et; item < 32 * kChunks; item += kCpEpiThreads) {
                     const int pp = item / kChunks, ch = item - pp * kChunks;
                     const int oyl = pp >> 2, oxl = pp & 3;
                     const int oy = ty * (kCpTileH / 2) + oyl, ox = tx * (kCpTileW / 2) + oxl;
@@ -239,7 +250,7 @@ conv_patch_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     *reinterpret_cast<uint4*>(out + (((long long)b * OH + oy) * OW + ox) * p.ld16 + ch * 8) = m;
                 }
             } else {
-                for (int item = et; item < 128 * kChunks; item += 128) {
+                for (int item = et; item < 128 * kChunks; item += kCpEpiThreads) {
                     const int row = item / kChunks, ch = item - row * kChunks;
                     const int py = ty * kCpTileH + (row >> 3), px = tx * kCpTileW + (row & 7);
                     if (py >= OH || px >= OW) continue;

@@ -35,7 +35,18 @@ constexpr int kStPatchPitch = 16, kStPatchH = kStTileH + 2, kStPatchW = kStTileW
 constexpr int kStPatchPx = kStPatchH * kStPatchW;              // 180 pixels carry data
 constexpr int kStPatchBytes = kStPatchPitch * kStPatchH * 128;  // 36 KB
 constexpr int kStPatchStages = 2;
-constexpr int kStThreads = 448;  // producer, issuer, 4 epilogue warps, 8 stem-worker warps
+// epilogue warps of the second convolution: four.  They are busy 83 % of a tile (ncu source page: 17 % of their samples
+// wait for the accumulator), the eight workers 80 %, and the schedulers issue 60 % of the cycles: eight epilogue
+// warps (ST_EPI_WARPS=8, columns split in two) take issue slots from the workers and measured 3 % SLOWER
+// (5.63 vs 5.47 ms per step), whereas the same change speeds up conv_patch.cu, which has no workers, by 7 %.
+#ifndef ST_EPI_WARPS
+#define ST_EPI_WARPS 4
+#endif
+constexpr int kStEpiWarps = ST_EPI_WARPS;
+constexpr int kStEpiThreads = 32 * kStEpiWarps;
+constexpr int kStFirstWorker = 2 + kStEpiWarps;  // must keep (warp & 3) == 2 for the first worker warp
+static_assert((kStFirstWorker & 3) == 2, "worker warps start on TMEM lane quarter 2");
+constexpr int kStThreads = 64 + kStEpiThreads + 256;  // producer, issuer, epilogue warps, 8 stem-worker warps
 constexpr int kStWTapBytes = 64 * 128, kStWBytes = 9 * kStWTapBytes;  // second convolution: 72 KB resident
 constexpr int kStABytes = 2 * 128 * 128;                               // im2col rows of the patch: 2 M-tiles
 constexpr int kStW1Bytes = 64 * 128;                                   // first convolution as a [64 x 32] bf16 tile
@@ -48,7 +59,7 @@ constexpr uint32_t kStTmemCols = 512;
 static_assert(kStSmemBytes <= 227 * 1024, "shared memory budget");
 
 
-__device__ __forceinline__ void st_epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void st_epi_bar() { asm volatile("bar.sync 1, %0;" ::"n"(kStEpiThreads) : "memory"); }
 __device__ __forceinline__ void st_work_bar() { asm volatile("bar.sync 2, 256;" ::: "memory"); }
 __device__ __forceinline__ void st_build_bar() { asm volatile("bar.sync 3, 128;" ::: "memory"); }
 __device__ __forceinline__ uint32_t st_bf16x2_max(uint32_t a, uint32_t b) {
@@ -123,7 +134,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             mbar_init(patch_full + s, 8);
             mbar_init(patch_empty + s, 1);
             mbar_init(acc_full + s, 1);
-            mbar_init(acc_empty + s, 4);
+            mbar_init(acc_empty + s, kStEpiWarps);
         }
         fence_barrier_init();
     }
@@ -144,7 +155,10 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         const bool leader = elect_one();
-        constexpr uint32_t idesc = umma_idesc(128, 64, 1u, 0u, 0u);
+#ifndef CONV_TIMING_MMA_N  // timing experiments only (results are wrong for any value but 64): B-operand read share
+#define CONV_TIMING_MMA_N 64
+#endif
+        constexpr uint32_t idesc = umma_idesc(128, CONV_TIMING_MMA_N, 1u, 0u, 0u);
         const uint32_t w0 = smem_u32(sW), w1 = smem_u32(sW1), a_im = smem_u32(sA);
         // conv 1 -> 64 on the 180 patch pixels: 2 M-tiles x (K = 32).  Tile parity `par` selects the im2col
         // buffer (K columns [32 par, 32 par + 32) of the 128-byte rows) and the TMEM accumulator pair.
@@ -199,12 +213,12 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             __syncwarp();
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-    } else if (warp < 6) {
-        // ===================== epilogue of the second convolution (128 threads) =====================
+    } else if (warp < kStFirstWorker) {
+        // ===================== epilogue of the second convolution (kStEpiThreads threads) =====================
         // phase A: thread <-> pixel row: TMEM -> bias/ReLU/BN -> bf16 -> swizzled staging tile in smem
         // phase B: thread <-> (output pixel, 16-byte chunks): optional 2x2 max, coalesced NHWC stores
-        const int quarter = warp & 3;
-        const int et = threadIdx.x - 64;  // 0..127
+        const int quarter = warp & 3, grp = (warp - 2) >> 2;  // TMEM lane quarter; 32-column group of the warp
+        const int et = threadIdx.x - 64;  // 0 .. kStEpiThreads - 1
         const int r_in_tile = quarter * 32 + lane;
         const bool pool = p.pool != 0;
         const int OH = pool ? (p.H >> 1) : p.H, OW = pool ? (p.W >> 1) : p.W;
@@ -220,6 +234,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             uint8_t* my_row = sStage + r_in_tile * 128;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
+                if (kStEpiWarps == 8 && c != grp) continue;  // warp-uniform; `c` stays a compile-time constant below
                 tmem_ld32(taddr + c * 32, r);
                 tmem_ld_wait();
                 uint32_t pk[16];
@@ -244,7 +259,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
             st_epi_bar();
             if (pool) {
                 // 32 pooled pixels x 8 chunks
-                for (int item = et; item < 32 * 8; item += 128) {
+                for (int item = et; item < 32 * 8; item += kStEpiThreads) {
                     const int pp = item >> 3, ch = item & 7;
                     const int oyl = pp >> 2, oxl = pp & 3;
                     const int oy = ty * (kStTileH / 2) + oyl, ox = tx * (kStTileW / 2) + oxl;
@@ -264,7 +279,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
                     *reinterpret_cast<uint4*>(p.out + (((long long)b * OH + oy) * OW + ox) * 64 + ch * 8) = m;
                 }
             } else {
-                for (int item = et; item < 128 * 8; item += 128) {
+                for (int item = et; item < 128 * 8; item += kStEpiThreads) {
                     const int row = item >> 3, ch = item & 7;
                     const int py = ty * kStTileH + (row >> 3), px = tx * kStTileW + (row & 7);
                     if (py >= OH || px >= OW) continue;
@@ -277,8 +292,8 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
     } else {
         // ===================== stem workers (128 threads) =====================
         const int quarter = warp & 3;
-        const int chalf = (warp - 6) >> 2;  // channels [32 chalf, 32 chalf + 32) in the TMEM -> patch pass
-        const int wt = threadIdx.x - 192;   // 0..255: staged image pixel / patch pixel (im2col row)
+        const int chalf = (warp - kStFirstWorker) >> 2;  // channels [32 chalf, 32 chalf + 32) in the TMEM -> patch pass
+        const int wt = threadIdx.x - 32 * kStFirstWorker;  // 0..255: staged image pixel / patch pixel (im2col row)
         if (wt < 128) {  // first convolution as a [64 channels x K = 32] bf16 tile: [w_hi | w_hi | w_lo | 0]
             const int n = wt >> 1, h = wt & 1;
             float f[32];
@@ -318,7 +333,7 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
         // the warps of quarters 2 / 3 (half the TMEM -> patch work) also build the im2col rows: `bt` numbers
         // their 128 threads.
         const bool builder = quarter >= 2;
-        const int bt = (((warp - 6) >> 2) * 2 + (quarter - 2)) * 32 + lane;
+        const int bt = (((warp - kStFirstWorker) >> 2) * 2 + (quarter - 2)) * 32 + lane;
         // gray pixel e (of 20 x 12) under the patch of tile t, zero outside the image
         // gray pixel e (of 20 x 12) under the patch of tile t, zero outside the image.  Returned RAW (float bits, or
         // the byte of a single-channel uint8 image) and converted by cook() where it is consumed: the request for the
