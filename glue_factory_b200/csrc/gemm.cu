@@ -30,7 +30,13 @@ constexpr int kTileH = 8, kTileW = 16;  // conv M-tile: 8 x 16 pixels
 constexpr int kEpiWarps = 8;
 constexpr int kEpiWarpsLn = 16;
 constexpr int kLnPartDefault = 128;  // measured in the step: 1.807 ms (128) vs 1.873 ms (256) per 18 launches
-__host__ __device__ constexpr int epi_warps(int epi) { return epi == EPI_LN_GELU ? kEpiWarpsLn : kEpiWarps; }
+// the QKV + rotary epilogue is instruction-bound too (86 us per launch against 49 us of MMAs with eight warps)
+#ifndef GEMM_QKV_EPI_WARPS
+#define GEMM_QKV_EPI_WARPS 16
+#endif
+__host__ __device__ constexpr int epi_warps(int epi) {
+    return epi == EPI_LN_GELU ? kEpiWarpsLn : epi == EPI_QKV_ROTARY ? GEMM_QKV_EPI_WARPS : kEpiWarps;
+}
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged in smem (bias | scale/gamma | shift/beta)
 // staging per epilogue warp: 32 rows x 128 B (fp32 row epilogues) or 32 rows x 64 B (bf16 rows: plain bf16 and
@@ -207,7 +213,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
         // gets the shared memory this saves.
         const int cj4 = lane & 3, rsub8 = lane >> 2;
 #pragma unroll 1
-        for (int c = half; c < BLOCK_N / 32; c += 2) {
+        for (int c = half; c < BLOCK_N / 32; c += epi_warps(EPI) / 4) {
             const int col0 = n0 + c * 32;
             if (col0 >= p.N) break;  // warp-uniform
             tmem_ld32(acc_taddr + c * 32, r);
@@ -251,7 +257,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
         return;
     }
 #pragma unroll 1
-    for (int c = half; c < BLOCK_N / 32; c += 2) {
+    for (int c = half; c < BLOCK_N / 32; c += epi_warps(EPI) / 4) {
         const int col0 = n0 + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
         // phase A: thread <-> accumulator row; raw accumulators into the swizzled staging tile
@@ -271,7 +277,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmParams& p, const EpiSmem
         }
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
         if (has_bias) bv = lds128(bias_s + (col0 + cj * 4) * 4);
-        if constexpr (EPI == EPI_RESID) load_aux(c + 2, aux_next);  // next chunk of this warp
+        if constexpr (EPI == EPI_RESID) load_aux(c + epi_warps(EPI) / 4, aux_next);  // next chunk of this warp
         const int col = col0 + cj * 4;
 #pragma unroll
         for (int it = 0; it < 8; ++it) {

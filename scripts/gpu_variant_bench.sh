@@ -9,7 +9,7 @@ for lib in "" $(ls glue_factory_b200/build/variants/libb200glue_*.so 2>/dev/null
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
 print('pairs/s', round(d['value'],1), 'ms/step', round(d['ms_per_step'],3))
-for k in d['kernels'][:6]: print('  %-24s %7.3f ms  x%d' % (k['tag'], k['ms_per_step'], k['launches_per_step']))
+for k in d['kernels'][:10]: print('  %-24s %7.3f ms  x%d' % (k['tag'], k['ms_per_step'], k['launches_per_step']))
 " >> $LOG 2>&1
 done
 cat $LOG
