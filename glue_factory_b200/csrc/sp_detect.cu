@@ -36,30 +36,35 @@ __device__ __forceinline__ uint32_t order_key32(float v) {
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-// o[i] = max(v[i .. i+2R]) for i < kSeg
+// three-input maximum (FMNMX3 on sm_100: same issue rate as the two-input form)
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
+// o[i] = max(v[i .. i+2R]) for i < kSeg: sliding maxima of three, combined three at a time
+// (R = 3: 20 + 16 instructions per 16 outputs instead of 56 two-input ones)
 template <int R>
 __device__ __forceinline__ void window_max(const float (&v)[kSeg + 2 * R], float (&o)[kSeg]) {
     constexpr int n = kSeg + 2 * R;
-    float m2[n - 1];
-#pragma unroll
-    for (int i = 0; i < n - 1; ++i) m2[i] = fmaxf(v[i], v[i + 1]);
     if constexpr (R == 1) {
 #pragma unroll
-        for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(m2[i], v[i + 2]);
+        for (int i = 0; i < kSeg; ++i) o[i] = fmax3(v[i], v[i + 1], v[i + 2]);
     } else {
-        float m4[n - 3];
+        float m3[n - 2];
 #pragma unroll
-        for (int i = 0; i < n - 3; ++i) m4[i] = fmaxf(m2[i], m2[i + 2]);
+        for (int i = 0; i < n - 2; ++i) m3[i] = fmax3(v[i], v[i + 1], v[i + 2]);
         if constexpr (R == 2) {
 #pragma unroll
-            for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(m4[i], v[i + 4]);
+            for (int i = 0; i < kSeg; ++i) o[i] = fmax3(m3[i], v[i + 3], v[i + 4]);
         } else if constexpr (R == 3) {
 #pragma unroll
-            for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(m4[i], m4[i + 3]);
+            for (int i = 0; i < kSeg; ++i) o[i] = fmax3(m3[i], m3[i + 3], v[i + 6]);
         } else {
             static_assert(R == 4, "radius 1..4");
 #pragma unroll
-            for (int i = 0; i < kSeg; ++i) o[i] = fmaxf(fmaxf(m4[i], m4[i + 4]), v[i + 8]);
+            for (int i = 0; i < kSeg; ++i) o[i] = fmax3(m3[i], m3[i + 3], m3[i + 6]);
         }
     }
 }
@@ -100,12 +105,19 @@ __device__ __forceinline__ void row_pass(const float* __restrict__ s, float* __r
 // by the thread that computed it.
 
 // column pass + comparison: bit(y, x) = s == max_{|dy|<=R} tmp(y+dy, x) [and not suppressed]
+// (wx0, wy0) = image coordinates of the staged window's first pixel: pixels outside the image (staged as -inf, where
+// a window of nothing but padding would compare equal) are masked by position, one AND per halfword instead of a
+// second comparison per pixel.
 template <int R, bool ROUND>
 __device__ __forceinline__ void col_pass(const float* __restrict__ s, const float* __restrict__ tmp,
-                                         uint16_t* __restrict__ maskh, const uint16_t* __restrict__ supph) {
+                                         uint16_t* __restrict__ maskh, const uint16_t* __restrict__ supph, int wx0, int wy0,
+                                         int H, int W) {
     using G = NmsGeom<R>;
     for (int item = threadIdx.x; item < kEW * (kEH / kSeg); item += kNmsFastThreads) {
         const int x = item & (kEW - 1), h = item / kEW, y0 = h * kSeg;
+        const int gy = wy0 + y0, gx = wx0 + x;
+        const int lo = max(0, -gy), hi = min(kSeg, H - gy);  // rows [lo, hi) of this halfword lie inside the image
+        const uint32_t inside = (gx >= 0 && gx < W && hi > lo) ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
         float v[kSeg + 2 * R], o[kSeg];
 #pragma unroll
         for (int j = 0; j < kSeg + 2 * R; ++j) v[j] = tmp[(y0 + j) * G::kPitchT + x];
@@ -114,8 +126,9 @@ __device__ __forceinline__ void col_pass(const float* __restrict__ s, const floa
 #pragma unroll
         for (int i = 0; i < kSeg; ++i) {
             const float sv = s[(y0 + i) * G::kPitchS + R + x];
-            bits |= (sv != -INFINITY && sv == o[i]) ? (1u << i) : 0u;  // out-of-image pixels never become maxima
+            bits |= (sv == o[i]) ? (1u << i) : 0u;
         }
+        bits &= inside;  // out-of-image pixels never become maxima
         uint16_t* m = maskh + h * G::kPitchM + R + x;
         if constexpr (ROUND) *m = (uint16_t)(*m | (bits & ~(uint32_t)supph[h * G::kPitchM + R + x]));
         else *m = (uint16_t)bits;
@@ -199,7 +212,7 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const i
 
     row_pass<R>(s, tmp);
     __syncthreads();
-    col_pass<R, false>(s, tmp, maskh, nullptr);
+    col_pass<R, false>(s, tmp, maskh, nullptr, x0, y0, H, W);
     __syncthreads();
 #pragma unroll 1
     for (int round = 0; round < 2; ++round) {
@@ -207,7 +220,7 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const i
         __syncthreads();
         row_pass<R>(s, tmp);
         __syncthreads();
-        col_pass<R, true>(s, tmp, maskh, supph);
+        col_pass<R, true>(s, tmp, maskh, supph, x0, y0, H, W);
         __syncthreads();
     }
 
