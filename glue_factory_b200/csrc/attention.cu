@@ -620,6 +620,10 @@ int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtenso
     const double t_n = (double)((items_n + num_sms - 1) / num_sms) * 1.0;
     const double t_w = (double)((items_w + num_sms - 1) / num_sms) * 2.0 * kWideGain;
     bool wide = t_w <= t_n;
+    // Device-side lengths = the adaptive path, whose stop / prune decisions compare against thresholds: there a batch
+    // must reproduce its pairs run one by one bit for bit (tests/test_gpu_adaptive.py), so the layout, which fixes the
+    // summation order of the softmax, must not depend on how many pairs share the launch.
+    if (p.len_override != nullptr) wide = false;
     if (att_layout_override() >= 0) wide = att_layout_override() == 1;
     if (wide) {
         p.q_tiles = qt_w;
