@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 TAG="${1:-attn}"; LAYOUT="${2:-wide}"
 export B200GLUE_ATT_LAYOUT=$LAYOUT
 python scripts/bench_attention.py 64 2048 5 || exit 1
-ncu --set full --import-source on --clock-control none -k regex:attention_tcgen05 -s 4 -c 1 -f -o gpurun_out/att_$TAG python scripts/bench_attention.py 64 2048 3 > gpurun_out/att_ncu_$TAG.log 2>&1; echo "capture exit=$?"
+ncu --set full --import-source on --clock-control none -k regex:attention_ -s 4 -c 1 -f -o gpurun_out/att_$TAG python scripts/bench_attention.py 64 2048 3 > gpurun_out/att_ncu_$TAG.log 2>&1; echo "capture exit=$?"
 ncu -i gpurun_out/att_$TAG.ncu-rep --page source --csv --print-source sass > gpurun_out/att_source_$TAG.csv 2>gpurun_out/att_source_$TAG.err
 ncu -i gpurun_out/att_$TAG.ncu-rep --page raw --csv > gpurun_out/att_raw_$TAG.csv 2>/dev/null
 ncu -i gpurun_out/att_$TAG.ncu-rep --page details > gpurun_out/att_details_$TAG.txt 2>/dev/null
