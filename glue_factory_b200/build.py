@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200glue.so")
-SOURCES = ["api.cu", "gemm.cu", "attention.cu", "attention_db.cu", "conv_patch.cu", "conv_stem.cu", "sp_kernels.cu", "sp_select.cu", "sp_detect.cu", "lg_kernels.cu", "lg_assign.cu", "lg_adaptive.cu", "lg_adaptive_batched.cu", "sg_sinkhorn.cu", "sg_kernels.cu", "io_kernels.cu", "eval_kernels.cu"]
+SOURCES = ["api.cu", "gemm.cu", "attention.cu", "conv_patch.cu", "conv_stem.cu", "sp_kernels.cu", "sp_select.cu", "sp_detect.cu", "lg_kernels.cu", "lg_assign.cu", "lg_adaptive.cu", "lg_adaptive_batched.cu", "sg_sinkhorn.cu", "sg_kernels.cu", "io_kernels.cu", "eval_kernels.cu"]
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "--expt-extended-lambda", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC",

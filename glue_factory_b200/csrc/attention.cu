@@ -466,12 +466,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
 static int att_layout_override() {  // read per call (a getenv is nanoseconds): tests switch it inside one process
     const char* e = getenv("B200GLUE_ATT_LAYOUT");
     if (!e) return -1;
-    return e[0] == 'w' ? 1 : e[0] == 'n' ? 0 : e[0] == 'd' ? 2 : -1;
+    return e[0] == 'w' ? 1 : e[0] == 'n' ? 0 : -1;
 }
-
-// attention_db.cu: two streams per CTA with a double-buffered S (items of 256 queries)
-int launch_attention_db(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p, int num_seqs,
-                        int max_q_len, int heads, int num_sms, cudaStream_t stream);
 
 template <bool WIDE>
 static int launch_attention_as(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, AttnParams p,
@@ -506,7 +502,6 @@ int launch_attention(const CUtensorMap& tq, const CUtensorMap& tk, const CUtenso
     // must reproduce its pairs run one by one bit for bit (tests/test_gpu_adaptive.py), so the layout, which fixes the
     // summation order of the softmax, must not depend on how many pairs share the launch.
     if (p.len_override != nullptr) wide = false;
-    if (att_layout_override() == 2) return launch_attention_db(tq, tk, tv, p, num_seqs, max_q_len, heads, num_sms, stream);
     if (att_layout_override() >= 0) wide = att_layout_override() == 1;
     if (wide) {
         p.q_tiles = qt_w;

@@ -1,5 +1,5 @@
-// Shared pieces of the attention kernels (attention.cu: four single-buffered streams; attention_db.cu: two streams with
-// a double-buffered S): tile geometry, packed fp32x2 arithmetic, the polynomial exp2, work-item decoding.
+// Pieces of the attention kernel (attention.cu) that are not the kernel itself: tile geometry, packed fp32x2
+// arithmetic, the polynomial exp2, work-item decoding.
 #pragma once
 #include "common.cuh"
 #include "attention.cuh"

@@ -212,7 +212,7 @@ def _attn_ref(q, k, v, scale):
     return torch.softmax(s, -1) @ v.float()
 
 
-@pytest.mark.parametrize("layout", ["narrow", "wide", "db", "auto"])
+@pytest.mark.parametrize("layout", ["narrow", "wide", "auto"])
 @pytest.mark.parametrize("lens", [[(128, 128)], [(200, 333), (77, 130)], [(2048, 2048)], [(129, 64), (256, 257), (300, 1)],
                                   [(513, 700), (1, 5), (640, 384)], [(1100, 900)] * 16 + [(385, 70), (40, 0), (900, 64)]])
 def test_attention(dev, lens, layout, monkeypatch):
@@ -261,7 +261,7 @@ def test_attention_live_lengths(dev, monkeypatch):
     seqs = ops.make_attn_seqs([(i * n, n, i * n, n, i, i) for i in range(len(live))], dev)
     lens = torch.tensor(live, dtype=torch.int32, device=dev)
     outs = {}
-    for layout in ("narrow", "wide", "db"):
+    for layout in ("narrow", "wide"):
         monkeypatch.setenv("B200GLUE_ATT_LAYOUT", layout)
         out = torch.full((len(live) * n, 256), 7.0, dtype=torch.bfloat16, device=dev)
         ops.attention(x, x, x, seqs, num_seqs=len(live), max_q_len=n, heads=H, ldq=768, ldk=768, ldv=768, q_col0=0,
