@@ -204,17 +204,29 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
                      "gemm: softmax/depth-to-space epilogue needs N == 65, block_n == 80 and the cell grid");
 
     CUtensorMap ta, tb;
-    if (d->conv && d->Cin == 64 && d->N == 64 && epi == B200_EPI_CONV_RELU_BN && d->K == 576 &&
-        d->ldb == 576 && env_int("B200_CONV_PATCH", 1) != 0) {
-        // C_in = 64 layers: halo patch loaded once per tile, nine taps addressed inside it (conv_patch.cu)
+    if (d->conv && d->Cin == 64 && epi == B200_EPI_CONV_RELU_BN && d->K == 576 && d->ldb == 576 &&
+        env_int("B200_CONV_PATCH", 1) != 0 &&
+        (d->N == 64 || (d->N == 128 && env_int("B200_CONV_PATCH_SPLIT", 1) != 0))) {
+        // C_in = 64 layers: halo patch loaded once per tile, nine taps addressed inside it (conv_patch.cu).  C_out = 128
+        // (64 -> 128) runs as two passes over 64 output channels each: the patch is read twice (72 KB per tile) where the
+        // generic implicit GEMM fetches its A tile nine times (144 KB), 0.76 -> see DESIGN.md 5.1
         p.H = d->H; p.W = d->W; p.Cin = 64;
         p.tiles_x = (d->W + 7) / 8; p.tiles_y = (d->H + 15) / 16;
         const uint64_t dims[4] = {64, (uint64_t)d->W, (uint64_t)d->H, (uint64_t)d->batch};
         const uint64_t strides[3] = {128, (uint64_t)d->W * 128, (uint64_t)d->H * d->W * 128};
         const uint32_t box[4] = {64, 16, 18, 1};
         if (make_map(&ta, d->a, 4, dims, strides, box) != 0) return -1;
-        if (make_map_2d(&tb, d->b, d->N, 576, 576, (uint32_t)d->N) != 0) return -1;
-        return launch_conv_patch(d->N, ta, tb, p, num_sms, stream);
+        for (int j = 0; j < d->N / 64; ++j) {
+            GemmParams pj = p;
+            pj.bias = p.bias + 64 * j;
+            pj.scale = p.scale + 64 * j;
+            pj.shift = p.shift + 64 * j;
+            pj.out16 = static_cast<__nv_bfloat16*>(p.out16) + 64 * j;  // ld16 stays the full row width
+            const __nv_bfloat16* wj = static_cast<const __nv_bfloat16*>(d->b) + (size_t)64 * j * 576;
+            if (make_map_2d(&tb, wj, 64, 576, 576, 64u) != 0) return -1;
+            if (launch_conv_patch(64, ta, tb, pj, num_sms, stream) != 0) return -1;
+        }
+        return 0;
     }
     const uint32_t b_box = epi == EPI_LN_GELU ? (uint32_t)ln_part_cols() : d->block_n > 256 ? 256u : (uint32_t)d->block_n;
     if (make_map_2d(&tb, d->b, d->b_rows, d->K, d->ldb, b_box) != 0) return -1;

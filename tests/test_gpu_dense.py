@@ -123,7 +123,7 @@ def test_similarity_batched(dev, B, M, N):
 
 
 @pytest.mark.parametrize("cin,cout,H,W,pool", [(64, 64, 40, 48, 1), (64, 64, 37, 53, 0), (64, 128, 24, 40, 0),
-                                               (128, 128, 19, 21, 1), (128, 512, 16, 24, 0)])
+                                               (64, 128, 37, 53, 1), (128, 128, 19, 21, 1), (128, 512, 16, 24, 0)])
 def test_conv3x3_relu_bn_pool(dev, cin, cout, H, W, pool):
     from glue_factory_b200 import ops
 
