@@ -159,6 +159,9 @@ conv_stem_kernel(const __grid_constant__ CUtensorMap tmap_w, const StemParams p)
 #define CONV_TIMING_MMA_N 64
 #endif
         constexpr uint32_t idesc = umma_idesc(128, CONV_TIMING_MMA_N, 1u, 0u, 0u);
+        // (descriptors are rebuilt per MMA here on purpose: with the linear form of conv_patch.cu, which issues the 36 MMAs
+        // of a tile in a burst, this kernel measured 11 % SLOWER, 6.06 vs 5.45 ms per step: its workers and epilogue warps
+        // pace it, and a tensor pipe that reads shared memory back to back takes bandwidth from them)
         const uint32_t w0 = smem_u32(sW), w1 = smem_u32(sW1), a_im = smem_u32(sA);
         // conv 1 -> 64 on the 180 patch pixels: 2 M-tiles x (K = 32).  Tile parity `par` selects the im2col
         // buffer (K columns [32 par, 32 par + 32) of the 128-byte rows) and the TMEM accumulator pair.

@@ -34,8 +34,15 @@ constexpr int kLnPartDefault = 128;  // measured in the step: 1.807 ms (128) vs 
 #ifndef GEMM_QKV_EPI_WARPS
 #define GEMM_QKV_EPI_WARPS 16
 #endif
+#ifndef GEMM_BIAS_EPI_WARPS
+#define GEMM_BIAS_EPI_WARPS 8
+#endif
+#ifndef GEMM_RESID_EPI_WARPS
+#define GEMM_RESID_EPI_WARPS 8
+#endif
 __host__ __device__ constexpr int epi_warps(int epi) {
-    return epi == EPI_LN_GELU ? kEpiWarpsLn : epi == EPI_QKV_ROTARY ? GEMM_QKV_EPI_WARPS : kEpiWarps;
+    return epi == EPI_LN_GELU ? kEpiWarpsLn : epi == EPI_QKV_ROTARY ? GEMM_QKV_EPI_WARPS
+         : epi == EPI_BIAS_BF16 ? GEMM_BIAS_EPI_WARPS : epi == EPI_RESID ? GEMM_RESID_EPI_WARPS : kEpiWarps;
 }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 constexpr int kParamFloats = 3 * 768;   // per-column epilogue operands staged in smem (bias | scale/gamma | shift/beta)
