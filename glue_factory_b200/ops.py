@@ -137,7 +137,11 @@ def gemm(a, w, *, M, N, K, lda, block_n, epilogue, a_rows=None, a_col0=0, ldb=No
         tag, work = f"conv3x3_{conv[2]}to{N}", 2.0 * batch * conv[0] * conv[1] * N * K
     else:
         tag, work = f"gemm_epi{epilogue}_n{N}_k{K}", 2.0 * batch * M * N * K
-    with _timed(tag, 1, work):
+    # kernels behind the call: C_in = 64 -> 128 runs as two halo-patch passes (csrc/api.cu)
+    launches = 2 if (conv is not None and conv[2] == 64 and N == 128 and epilogue == EPI_CONV_RELU_BN and
+                     os.environ.get("B200_CONV_PATCH", "1") != "0" and
+                     os.environ.get("B200_CONV_PATCH_SPLIT", "1") != "0") else 1
+    with _timed(tag, launches, work):
         _lib.check(_lib.lib().b200_gemm(C.byref(d), _stream()))
 
 
