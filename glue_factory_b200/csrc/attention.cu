@@ -98,6 +98,8 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gri
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    pdl_wait();     // predecessor grid complete, its writes visible (the prologue above overlapped its tail)
+    pdl_trigger();  // successor may become resident
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -480,8 +482,8 @@ static int launch_attention_as(const CUtensorMap& tq, const CUtensorMap& tk, con
     }
     p.num_items = (int)items;
     const int grid = (int)(items < num_sms ? items : num_sms);
-    attention_tcgen05_kernel<WIDE><<<grid, kAttThreads, AttCfg<WIDE>::kSmemBytes, stream>>>(tq, tk, tv, p);
-    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(launch_pdl(attention_tcgen05_kernel<WIDE>, dim3(grid), dim3(kAttThreads), AttCfg<WIDE>::kSmemBytes, stream,
+                               tq, tk, tv, p));
     return 0;
 }
 
