@@ -233,32 +233,36 @@ nms_list_kernel(const float* __restrict__ scores, int H, int W, int pad, const i
     unsigned long long* rec = reinterpret_cast<unsigned long long*>(s);
     static_assert((size_t)G::kTileW * G::kTileH * 8 <= (size_t)(G::kSFloats + G::kTFloats) * 4,
                   "candidate records must fit the window + scratch");
-    // one warp per output row segment of 32 columns; the maxima's scores come from global memory (the staged copy
+    // the maxima's scores come from global memory (the staged copy
     // was overwritten by the suppression): a few percent of the pixels, L2 hits
-    constexpr int kSegs = (G::kTileW + 31) / 32;
-    for (int item = warp; item < G::kTileH * kSegs; item += kNmsFastThreads / 32) {
-        const int ty = item / kSegs, tx = (item - ty * kSegs) * 32 + lane;
+    // the tile's pixels as one linear index space (98 x 66 for R = 3: whole warps of consecutive pixels; row-wise
+    // segments of 32 would leave the fourth segment of every row with 2 live lanes)
+    constexpr int kTilePx = G::kTileW * G::kTileH;
+    const bool has_border = pad > 0;
+    for (int base = warp * 32; base < kTilePx; base += kNmsFastThreads) {
+        const int i = base + lane;
+        const int ty = i / G::kTileW, tx = i - ty * G::kTileW;
         const int y = oy + ty, x = ox + tx;
-        const bool valid = tx < G::kTileW && y < H && x < W;
-        const int ex = tx + 5 * R, ey = ty + 5 * R;
+        const bool valid = i < kTilePx && y < H && x < W;
         float v = 0.f;
         bool keep = false;
         if (valid) {
+            const int ex = tx + 5 * R, ey = ty + 5 * R;
+            const int gi = y * W + x;  // < 2^31: one score map
             const bool mx = (maskh[(ey >> 4) * G::kPitchM + R + ex] >> (ey & 15)) & 1u;
-            if (mx) v = __ldg(src + (long long)y * W + x);
-            const bool border = pad > 0 && (y < pad || x < pad || y >= bh - pad || x >= bw - pad);
-            if (border) v = -1.f;
-            dst[(long long)y * W + x] = v;
+            if (mx) v = __ldg(src + gi);
+            if (has_border && (y < pad || x < pad || y >= bh - pad || x >= bw - pad)) v = -1.f;
+            dst[gi] = v;
             keep = v > 0.f;
         }
         if (list != nullptr) {
             const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
             if (ballot != 0u) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&s_count, __popc(ballot));
-                base = __shfl_sync(0xffffffffu, base, 0);
+                int slot = 0;
+                if (lane == 0) slot = atomicAdd(&s_count, __popc(ballot));
+                slot = __shfl_sync(0xffffffffu, slot, 0);
                 if (keep)
-                    rec[base + __popc(ballot & ((1u << lane) - 1u))] =
+                    rec[slot + __popc(ballot & ((1u << lane) - 1u))] =
                         (static_cast<unsigned long long>(order_key32(v)) << 32) | ~static_cast<uint32_t>(y * W + x);
             }
         }
