@@ -244,7 +244,10 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
         if (make_map(&ta, d->a, 4, dims, strides, box) != 0) return -1;
     } else {
         B200_REQUIRE(d->M >= 1, "gemm: M=%d", d->M);
-        if (make_map_2d(&ta, d->a, d->a_rows, d->K, d->lda, 128) != 0) return -1;
+#ifndef GEMM_TIMING_LN_A_ROWS  // timing experiments only (wrong results below 128): operand-feed share of the LN GEMM
+#define GEMM_TIMING_LN_A_ROWS 128
+#endif
+        if (make_map_2d(&ta, d->a, d->a_rows, d->K, d->lda, epi == EPI_LN_GELU ? GEMM_TIMING_LN_A_ROWS : 128) != 0) return -1;
     }
     return launch_gemm(d->block_n, epi, a_mode, ta, tb, p, num_sms, stream);
 }

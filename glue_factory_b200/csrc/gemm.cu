@@ -639,7 +639,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 uint8_t* sa = smem + stage * Cfg::kStageBytes;
                 uint8_t* sb = sa + Cfg::kABytes;
                 if (leader) {
-                    mbar_arrive_expect_tx(full_bar + stage, Cfg::kStageBytes);
+#ifndef GEMM_TIMING_LN_A_ROWS
+#define GEMM_TIMING_LN_A_ROWS 128
+#endif
+                    mbar_arrive_expect_tx(full_bar + stage,
+                                          Cfg::kStageBytes - (EPI == EPI_LN_GELU ? (128 - GEMM_TIMING_LN_A_ROWS) * 128 : 0));
                     if constexpr (A_MODE == 0) {
                         tma_load_2d(sa, &tmap_a, full_bar + stage, kb * kBlockK, b * p.a_batch_rows + mt * kBlockM);
                     } else {
