@@ -389,8 +389,16 @@ __device__ __forceinline__ void ln_gelu_half(const GemmParams& p, const EpiSmem&
             const float4 be = lds128(be_s + off);
             const f32x2 xa = add2(pk2(__uint_as_float(r[q * 4]), __uint_as_float(r[q * 4 + 1])), pk2(b.x, b.y));
             const f32x2 xb = add2(pk2(__uint_as_float(r[q * 4 + 2]), __uint_as_float(r[q * 4 + 3])), pk2(b.z, b.w));
+#ifndef GEMM_TIMING_LN_EPI  // timing experiments only: 1 = no GELU, 2 = neither statistics nor GELU (wrong results)
+#define GEMM_TIMING_LN_EPI 0
+#endif
+#if GEMM_TIMING_LN_EPI == 0
             const f32x2 ya = gelu_erf2(fma2(fma2(xa, rstd2, nmr2), pk2(g.x, g.y), pk2(be.x, be.y)));
             const f32x2 yb = gelu_erf2(fma2(fma2(xb, rstd2, nmr2), pk2(g.z, g.w), pk2(be.z, be.w)));
+#else
+            const f32x2 ya = fma2(fma2(xa, rstd2, nmr2), pk2(g.x, g.y), pk2(be.x, be.y));
+            const f32x2 yb = fma2(fma2(xb, rstd2, nmr2), pk2(g.z, g.w), pk2(be.z, be.w));
+#endif
             float y0, y1, y2, y3;
             upk2(ya, y0, y1);
             upk2(yb, y2, y3);
@@ -749,7 +757,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                 for (int h = 0; h < Cfg::kAccStages; ++h) {
                     mbar_wait(acc_full + h, acc_phase);
                     tc_fence_after();
+#if !defined(GEMM_TIMING_LN_EPI) || GEMM_TIMING_LN_EPI != 2
                     ln_stats_half<BLOCK_N>(es, lane_taddr + h * BLOCK_N, h * BLOCK_N, half, sum, sumsq);
+#endif
                 }
                 float2* exch = es.exch + (acc_phase & 1) * 512;
                 exch[half * 128 + r_in_tile] = make_float2(sum, sumsq);
