@@ -228,11 +228,7 @@ int b200_gemm(const b200_gemm_desc* d, b200_stream_t stream_) {
         }
         return 0;
     }
-#ifndef GEMM_TIMING_LN_B_DIV  // timing experiments only (wrong results above 1): weight-tile share of the LN GEMM's feed
-#define GEMM_TIMING_LN_B_DIV 1
-#endif
-    const uint32_t b_box = epi == EPI_LN_GELU ? (uint32_t)ln_part_cols() / GEMM_TIMING_LN_B_DIV
-                                              : d->block_n > 256 ? 256u : (uint32_t)d->block_n;
+    const uint32_t b_box = epi == EPI_LN_GELU ? (uint32_t)ln_part_cols() : d->block_n > 256 ? 256u : (uint32_t)d->block_n;
     if (make_map_2d(&tb, d->b, d->b_rows, d->K, d->ldb, b_box) != 0) return -1;
     int a_mode = 0;
     if (d->conv) {
